@@ -1,0 +1,432 @@
+// tcgen05 / TMEM / TMA bf16 GEMM for sm_100a with fused epilogues.
+//
+//   D[M,N] = epilogue( A[M,K] * B[N,K]^T )      fp32 accumulation in tensor memory
+//
+// Each operand may be K-major (row-major [rows, K]) or MN-major (row-major [K, rows]), which
+// gives the three layouts a linear layer needs without any transpose pass:
+//   forward  Y  = X  W^T         A K-major,  B K-major
+//   dgrad    dX = dY W           A K-major,  B MN-major
+//   wgrad    dW = dY^T X         A MN-major, B MN-major
+// Replaces the cuBLAS calls the reference reaches through nn.Linear / F.multi_head_attention
+// (benchmarking/train_harness.py:58,113-123,127) and their autograd backward GEMMs
+// (SURVEY.md §2.6 K3,K5-K8,K10).
+//
+// Structure: persistent, warp-specialised CTA of 192 threads, one CTA per SM.
+//   warp 0      TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
+//   warp 1      MMA issuer    (one elected lane: tcgen05.mma cta_group::1, M=128, N=BN, K=16)
+//   warps 2..5  epilogue      (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+// Two accumulator stages in TMEM (2*BN columns) let the epilogue of tile i overlap the main
+// loop of tile i+1.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "b200_internal.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 64;
+constexpr int GEMM_THREADS = 192;
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;  // 16 KiB
+  static constexpr int kBBytes = BN * GEMM_BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTmemCols = 2 * BN;  // 256 or 512, power of two
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + align slack
+};
+
+struct GemmParams {
+  int M, N, K;
+  int a_mn, b_mn;  // 1 = MN-major operand
+  int epi;         // B200_EPI_*
+  int ldd;         // leading dimension of D / out2 / aux / resid (elements)
+  __nv_bfloat16* D;
+  __nv_bfloat16* D2;            // second output (GELU activation)
+  const __nv_bfloat16* bias;    // [N]
+  const __nv_bfloat16* aux;     // residual or pre-activation, [M, ldd]
+  float drop_scale;             // 1/(1-p)
+  uint32_t drop_threshold;      // p * 2^32, 0 = no dropout
+  uint32_t drop_seed;
+  int num_m_tiles, num_n_tiles;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
+                         const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles need 1024-byte alignment.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* tiles = smem;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;                         // [kStages]
+  uint64_t* empty_bar = bars + Cfg::kStages;         // [kStages]
+  uint64_t* tfull_bar = bars + 2 * Cfg::kStages;     // [2]
+  uint64_t* tempty_bar = bars + 2 * Cfg::kStages + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
+        const int n0 = (tile / p.num_m_tiles) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = tiles + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          const int k0 = kb * GEMM_BK;
+          if (!p.a_mn) {
+            tma_load_2d(&map_a, &full_bar[stage], sa, k0, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < GEMM_BM / 64; ++c)
+              tma_load_2d(&map_a, &full_bar[stage], sa + c * (GEMM_BK * 128), m0 + 64 * c, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(&map_b, &full_bar[stage], sb, k0, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c)
+              tma_load_2d(&map_b, &full_bar[stage], sb + c * (GEMM_BK * 128), n0 + 64 * c, k0);
+          }
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, p.a_mn != 0, p.b_mn != 0);
+      // K-major: +32 B per 16-element K step inside the 128 B swizzle row.
+      // MN-major: +16 k-rows * 128 B = 2048 B per K step; MN chunks are BK*128 B apart.
+      const uint32_t a_kstep = p.a_mn ? 2048u : 32u;
+      const uint32_t b_kstep = p.b_mn ? 2048u : 32u;
+      const uint32_t a_lbo = p.a_mn ? GEMM_BK * 128u : 16u;
+      const uint32_t b_lbo = p.b_mn ? GEMM_BK * 128u : 16u;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(tiles + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < GEMM_BK / 16; ++k) {
+            const uint64_t adesc = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+            const uint64_t bdesc = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+            umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
+      const int n0 = (tile / p.num_m_tiles) * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const int row = m0 + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+      const size_t row_off = static_cast<size_t>(row) * p.ldd;
+      const uint32_t taddr_row =
+          tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr_row + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        if (row_ok && col0 < p.N) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {  // 8 columns (16 B of bf16) per group
+            const int col = col0 + g * 8;
+            if (col >= p.N) break;
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+            if (p.epi == B200_EPI_BIAS || p.epi == B200_EPI_BIAS_GELU ||
+                p.epi == B200_EPI_BIAS_RESID) {
+              const uint4 bv = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
+              const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(bw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+              }
+            }
+            if (p.epi == B200_EPI_BIAS_GELU) {
+              // pre-activation -> D, activation -> D2
+              uint4 o;
+              o.x = pack_bf16x2(v[0], v[1]);
+              o.y = pack_bf16x2(v[2], v[3]);
+              o.z = pack_bf16x2(v[4], v[5]);
+              o.w = pack_bf16x2(v[6], v[7]);
+              *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
+              o.x = pack_bf16x2(v[0], v[1]);
+              o.y = pack_bf16x2(v[2], v[3]);
+              o.z = pack_bf16x2(v[4], v[5]);
+              o.w = pack_bf16x2(v[6], v[7]);
+              *reinterpret_cast<uint4*>(p.D2 + row_off + col) = o;
+              continue;
+            }
+            if (p.epi == B200_EPI_BIAS_RESID) {
+              if (p.drop_threshold) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const uint64_t idx = static_cast<uint64_t>(row) * p.N + (col + j);
+                  v[j] = dropout_keep(p.drop_seed, idx, p.drop_threshold) ? v[j] * p.drop_scale
+                                                                          : 0.0f;
+                }
+              }
+              const uint4 xv = *reinterpret_cast<const uint4*>(p.aux + row_off + col);
+              const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(xw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+              }
+            } else if (p.epi == B200_EPI_DGELU) {
+              const uint4 xv = *reinterpret_cast<const uint4*>(p.aux + row_off + col);
+              const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(xw[j]);
+                v[2 * j] *= gelu_erf_grad(f.x);
+                v[2 * j + 1] *= gelu_erf_grad(f.y);
+              }
+            } else if (p.epi == B200_EPI_ACCUM) {
+              const uint4 xv = *reinterpret_cast<const uint4*>(p.D + row_off + col);
+              const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16x2(xw[j]);
+                v[2 * j] += f.x;
+                v[2 * j + 1] += f.y;
+              }
+            }
+            uint4 o;
+            o.x = pack_bf16x2(v[0], v[1]);
+            o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]);
+            o.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
+          }
+        }
+      }
+      // all tcgen05.ld of this warp are complete (wait::ld above): release the accumulator
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// host side
+// ----------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) !=
+            cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess) {
+      return nullptr;
+    }
+    fn = reinterpret_cast<PFN_encodeTiled>(ptr);
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor map over a row-major [rows, cols] matrix with leading dimension ld (elements),
+// box = [box_rows, box_cols], 128-byte swizzle (box_cols * 2 bytes must be <= 128).
+int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_rows, uint32_t box_cols) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return -1;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * sizeof(__nv_bfloat16)};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -static_cast<int>(r) - 1000;
+}
+
+int device_sm_count() {
+  static int sms[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+  return sms[dev];
+}
+
+template <int BN>
+static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, int max_ctas,
+                       cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_done[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::kSmemBytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_done[dev & 63] = true;
+  }
+  p.num_m_tiles = (p.M + GEMM_BM - 1) / GEMM_BM;
+  p.num_n_tiles = (p.N + BN - 1) / BN;
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  int grid = device_sm_count();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (tiles < grid) grid = tiles;
+  gemm_bf16_tcgen05_kernel<BN><<<grid, GEMM_THREADS, Cfg::kSmemBytes, stream>>>(ma, mb, p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int lda,
+                              int ldb, int ldd, int a_mn, int b_mn, int epi, const void* bias,
+                              const void* aux, void* D2, float drop_p, unsigned int drop_seed,
+                              int bn_hint, int max_ctas, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((N % 8) || (K % 8) || (lda % 8) || (ldb % 8) || (ldd % 8)) return -2;
+  if (a_mn && (M % 8)) return -2;
+  int BN = bn_hint;
+  if (BN != 128 && BN != 256) {
+    // Pick the tile width that wastes the fewest SM-waves.
+    const int sms = device_sm_count();
+    const int mt = (M + GEMM_BM - 1) / GEMM_BM;
+    const long t128 = static_cast<long>(mt) * ((N + 127) / 128);
+    const long t256 = static_cast<long>(mt) * ((N + 255) / 256);
+    const long w128 = (t128 + sms - 1) / sms;       // cost units: 1 per wave
+    const long w256 = 2 * ((t256 + sms - 1) / sms);  // a 256-wide tile costs two units
+    BN = (w256 <= w128 && N >= 256) ? 256 : 128;
+  }
+  CUtensorMap ma, mb;
+  int rc;
+  if (!a_mn)
+    rc = make_tmap_2d_bf16(&ma, A, M, K, lda, GEMM_BM, 64);
+  else
+    rc = make_tmap_2d_bf16(&ma, A, K, M, lda, GEMM_BK, 64);
+  if (rc) return rc;
+  if (!b_mn)
+    rc = make_tmap_2d_bf16(&mb, B, N, K, ldb, BN, 64);
+  else
+    rc = make_tmap_2d_bf16(&mb, B, K, N, ldb, GEMM_BK, 64);
+  if (rc) return rc;
+
+  GemmParams p;
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.a_mn = a_mn;
+  p.b_mn = b_mn;
+  p.epi = epi;
+  p.ldd = ldd;
+  p.D = static_cast<__nv_bfloat16*>(D);
+  p.D2 = static_cast<__nv_bfloat16*>(D2);
+  p.bias = static_cast<const __nv_bfloat16*>(bias);
+  p.aux = static_cast<const __nv_bfloat16*>(aux);
+  if (drop_p > 0.f && drop_p < 1.f) {
+    p.drop_scale = 1.0f / (1.0f - drop_p);
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
+  } else {
+    p.drop_scale = 1.0f;
+    p.drop_threshold = 0;
+  }
+  p.drop_seed = drop_seed;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (BN == 256) return launch_gemm<256>(ma, mb, p, max_ctas, s);
+  return launch_gemm<128>(ma, mb, p, max_ctas, s);
+}
