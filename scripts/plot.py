@@ -1,0 +1,8 @@
+#!/usr/bin/env python3
+"""CLI shim at the reference path scripts/plot.py -> b200bench.analysis.plot."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from b200bench.analysis.plot import main
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,57 @@
+"""CPU/gloo world_size=2 plumbing (first BASELINE.json config) and strategy equivalence."""
+import json
+import os
+import sys
+
+import pytest
+import torch
+
+from b200bench.launch import launch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+COMMON = ["--tier", "T", "--seq-len", "32", "--warmup-steps", "1", "--per-device-batch", "2",
+          "--device", "cpu", "--dropout", "0", "--log-interval", "0",
+          "--deepspeed-config", os.path.join(ROOT, "configs/deepspeed/zero2.json"),
+          "--fsdp-config", os.path.join(ROOT, "configs/fsdp/fsdp_config.yaml")]
+
+
+def _run(tmp_path, strategy, nproc, steps=4, extra=()):
+    out = tmp_path / f"{strategy}_{nproc}"
+    sd = out / "sd.pt"
+    rc = launch(nproc, ["--strategy", strategy, "--steps", str(steps), "--grad-accum", "1",
+                        "--results-dir", str(out), "--save-state-dict", str(sd)] + COMMON + list(extra),
+                timeout=240, env_extra={"PYTHONPATH": ROOT})
+    assert rc == 0
+    res = json.load(open(out / f"result_{strategy}_ws{nproc}_seq32_tierT.json"))
+    return res, torch.load(sd)
+
+
+def test_ddp_gloo_ws2_plumbing(tmp_path):
+    res, sd = _run(tmp_path, "ddp", 2)
+    assert res["world_size"] == 2 and res["tokens_per_sec"] > 0 and res["mean_loss"] > 0
+    assert list(res.keys())[:13] == ["strategy", "world_size", "rank", "seq_len", "tier", "steps",
+                                     "per_device_batch", "grad_accum", "tokens_per_sec", "mean_step_time_sec",
+                                     "mean_loss", "peak_vram_gb", "h2d_gbps_per_gpu"]
+    assert "lm_head.weight" in sd and len(sd) == 29
+
+
+def test_ddp_equals_fsdp_and_uniform_zero(tmp_path):
+    """Same data, dropout 0: after k steps DDP == FSDP == ZeRO-2 == ZeRO-3 parameters.
+    The ZeRO configs add clipping + WarmupLR, so they are compared with each other."""
+    _, ddp = _run(tmp_path, "ddp", 2)
+    _, fsdp = _run(tmp_path, "fsdp", 2)
+    for k in ddp:
+        assert torch.allclose(ddp[k], fsdp[k], atol=1e-6), k
+    _, z2 = _run(tmp_path, "zero2", 2, extra=["--grad-accum-mode", "uniform"])
+    z3cfg = ["--deepspeed-config", os.path.join(ROOT, "configs/deepspeed/zero3.json"),
+             "--grad-accum-mode", "uniform"]
+    _, z3 = _run(tmp_path, "zero3", 2, extra=z3cfg)
+    for k in z2:
+        assert torch.allclose(z2[k], z3[k], atol=1e-6), k
+
+
+def test_rank_failure_propagates(tmp_path):
+    rc = launch(2, ["--strategy", "zero2", "--steps", "2", "--grad-accum", "1", "--results-dir", str(tmp_path),
+                    "--tier", "T", "--seq-len", "32", "--per-device-batch", "1", "--device", "cpu",
+                    "--deepspeed-config", "/nonexistent.json"], timeout=120, env_extra={"PYTHONPATH": ROOT})
+    assert rc != 0
