@@ -1,0 +1,32 @@
+# Native build of b200bench for sm_100a.  `make` -> b200bench/lib/libb200bench.so (in-tree, so it
+# travels to the GPU box) and the standalone kernel harnesses under build/bin/.
+NVCC      ?= nvcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVCCFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo --use_fast_math -Xcompiler -fPIC -Xcompiler -Wall
+SRCS      := $(wildcard csrc/*.cu)
+OBJS      := $(patsubst csrc/%.cu,build/obj/%.o,$(SRCS))
+HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
+LIB       := b200bench/lib/libb200bench.so
+TESTS     := build/bin/test_gemm build/bin/test_attn
+
+all: $(LIB) $(TESTS)
+
+build/obj/%.o: csrc/%.cu $(HDRS)
+	@mkdir -p build/obj
+	$(NVCC) $(NVCCFLAGS) -c $< -o $@
+
+$(LIB): $(OBJS)
+	@mkdir -p b200bench/lib
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+
+build/bin/%: csrc/tests/%.cu $(OBJS)
+	@mkdir -p build/bin
+	$(NVCC) $(NVCCFLAGS) $< $(OBJS) -o $@
+
+ptxas-info:
+	@for f in $(SRCS); do echo "== $$f"; $(NVCC) $(NVCCFLAGS) -Xptxas -v -c $$f -o /dev/null 2>&1 | grep -E "registers|spill" ; done
+
+clean:
+	rm -rf build b200bench/lib
+
+.PHONY: all clean ptxas-info

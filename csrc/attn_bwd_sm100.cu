@@ -1,0 +1,412 @@
+// Fused attention backward for sm_100a (recompute-based, FlashAttention-2 style loop order) with
+// all five matrix products on tcgen05 tensor cores and their accumulators in tensor memory.
+//
+// The reference gets this through autograd over bmm/softmax/dropout/bmm and keeps the fp32
+// [B*H, T, T] probabilities alive for it (benchmarking/train_harness.py:127,374; SURVEY.md §2.6
+// K4, §5.7); here only O and the log-sum-exp are saved and P is recomputed tile by tile.
+//
+// CTA = one (batch, head, 128-key block j); it keeps K_j, V_j resident and streams the query
+// blocks i.  Everything is computed TRANSPOSED (rows = keys, columns = queries) so that each
+// thread owns one key row in tensor memory and writes its row of P^T / dS^T straight into the
+// 128B-swizzled K-major shared-memory layout the next MMAs consume:
+//   S^T  = K_j  Q_i^T          A = K_j (K-major)    B = Q_i  (K-major)    M128 N128 K64
+//   dP^T = V_j  dO_i^T         A = V_j (K-major)    B = dO_i (K-major)    M128 N128 K64
+//   dV_j += P^T  dO_i          A = P^T (K-major)    B = dO_i (MN-major)   M128 N64  K128
+//   dK_j += dS^T Q_i           A = dS^T (K-major)   B = Q_i  (MN-major)   M128 N64  K128
+//   dQ_i  = dS   K_j           A = dS^T buffer read MN-major,  B = K_j (MN-major)  M128 N64 K128
+// dQ_i is added to an fp32 accumulator in global memory (vector red.add) because every key block
+// contributes to it; a small kernel converts it to bf16 afterwards.
+//
+// 320 threads: warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 compute (two threads per key
+// row, each covering 64 of the 128 query columns).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b200_internal.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int AB_BLK = 128;
+constexpr int AB_HD = 64;
+constexpr int AB_THREADS = 320;
+constexpr int AB_TILE = AB_BLK * AB_HD * 2;    // 16 KiB
+constexpr int AB_PBYTES = AB_BLK * AB_BLK * 2; // 32 KiB
+constexpr int AB_SMEM = 2 * AB_TILE /*K,V*/ + 4 * AB_TILE /*Q,dO x2*/ + 2 * AB_PBYTES /*P,dS*/ +
+                        2 * AB_BLK * 4 /*lse,D*/ + 256 /*bars*/ + 1024 /*align*/;
+
+struct AttnBwdParams {
+  const float* lse;
+  const float* D;
+  float* dq_acc;
+  __nv_bfloat16* dqkv;
+  int B, T, H, d;
+  float scale, scale_log2;
+  int causal;
+  uint32_t drop_threshold;
+  float drop_scale;
+  uint32_t drop_seed;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(AB_THREADS, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
+                const __grid_constant__ CUtensorMap map_do, const AttnBwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + AB_TILE;
+  uint8_t* sQ = sV + AB_TILE;            // [2]
+  uint8_t* sDO = sQ + 2 * AB_TILE;       // [2]
+  uint8_t* sP = sDO + 2 * AB_TILE;       // P^T  [128 keys][128 queries] bf16, two 64-query chunks
+  uint8_t* sDS = sP + AB_PBYTES;         // dS^T same layout
+  float* sLSE = reinterpret_cast<float*>(sDS + AB_PBYTES);  // [128] (already times log2e)
+  float* sD = sLSE + AB_BLK;                                 // [128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sD + AB_BLK);
+  uint64_t* kv_full = bars;          // 1
+  uint64_t* qdo_full = bars + 1;     // [2]
+  uint64_t* qdo_empty = bars + 3;    // [2]
+  uint64_t* sdp_full = bars + 5;     // 1
+  uint64_t* pds_full = bars + 6;     // 1 (256 arrivals)
+  uint64_t* dq_full = bars + 7;      // 1
+  uint64_t* dq_empty = bars + 8;     // 1 (256 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nblk = (p.T + AB_BLK - 1) / AB_BLK;
+  const int jb = blockIdx.x % nblk;
+  const int bh = blockIdx.x / nblk;
+  const int b = bh / p.H, h = bh % p.H;
+  const int k0 = jb * AB_BLK;
+  const int row_base = b * p.T;
+  const int i_begin = p.causal ? jb : 0;   // causal: only query blocks at or after the key block
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_qkv);
+    tma_prefetch_desc(&map_do);
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&qdo_full[s], 1);
+      mbar_init(&qdo_empty[s], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(pds_full, 256);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_empty, 256);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t TC_S = 0, TC_DP = 128, TC_DV = 256, TC_DK = 320, TC_DQ = 384;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      const int qcol = h * AB_HD, kcol = p.d + h * AB_HD, vcol = 2 * p.d + h * AB_HD;
+      mbar_expect_tx(kv_full, 2 * AB_TILE);
+      tma_load_2d(&map_qkv, kv_full, sK, kcol, row_base + k0);
+      tma_load_2d(&map_qkv, kv_full, sV, vcol, row_base + k0);
+      int st = 0;
+      uint32_t ph = 0;
+      for (int i = i_begin; i < nblk; ++i) {
+        mbar_wait(&qdo_empty[st], ph ^ 1);
+        mbar_expect_tx(&qdo_full[st], 2 * AB_TILE);
+        tma_load_2d(&map_qkv, &qdo_full[st], sQ + st * AB_TILE, qcol, row_base + i * AB_BLK);
+        tma_load_2d(&map_do, &qdo_full[st], sDO + st * AB_TILE, h * AB_HD, row_base + i * AB_BLK);
+        if (++st == 2) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      const uint32_t id_sdp = umma_idesc_bf16(AB_BLK, AB_BLK, false, false);
+      const uint32_t id_dvk = umma_idesc_bf16(AB_BLK, AB_HD, false, true);
+      const uint32_t id_dq = umma_idesc_bf16(AB_BLK, AB_HD, true, true);
+      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP), aDS = smem_u32(sDS);
+      mbar_wait(kv_full, 0);
+      tc_fence_after();
+      int st = 0;
+      uint32_t ph = 0, it_ph = 0;
+      for (int i = i_begin; i < nblk; ++i) {
+        mbar_wait(&qdo_full[st], ph);
+        tc_fence_after();
+        const uint32_t aQ = smem_u32(sQ + st * AB_TILE), aDO = smem_u32(sDO + st * AB_TILE);
+#pragma unroll
+        for (int k = 0; k < AB_HD / 16; ++k)
+          umma_bf16_ss(tmem_base + TC_S, umma_smem_desc(aK + k * 32, 16, 1024),
+                       umma_smem_desc(aQ + k * 32, 16, 1024), id_sdp, k ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < AB_HD / 16; ++k)
+          umma_bf16_ss(tmem_base + TC_DP, umma_smem_desc(aV + k * 32, 16, 1024),
+                       umma_smem_desc(aDO + k * 32, 16, 1024), id_sdp, k ? 1u : 0u);
+        umma_commit(sdp_full);
+        mbar_wait(pds_full, it_ph);        // P^T and dS^T are in shared memory
+        mbar_wait(dq_empty, it_ph ^ 1);    // previous dQ tile has been drained
+        tc_fence_after();
+        const uint32_t acc = (i > i_begin) ? 1u : 0u;
+#pragma unroll
+        for (int k = 0; k < AB_BLK / 16; ++k) {
+          const uint32_t a_off = (k >> 2) * (AB_BLK * 128) + (k & 3) * 32;
+          umma_bf16_ss(tmem_base + TC_DV, umma_smem_desc(aP + a_off, 16, 1024),
+                       umma_smem_desc(aDO + k * 2048, AB_BLK * 128, 1024), id_dvk, (k ? 1u : acc));
+        }
+#pragma unroll
+        for (int k = 0; k < AB_BLK / 16; ++k) {
+          const uint32_t a_off = (k >> 2) * (AB_BLK * 128) + (k & 3) * 32;
+          umma_bf16_ss(tmem_base + TC_DK, umma_smem_desc(aDS + a_off, 16, 1024),
+                       umma_smem_desc(aQ + k * 2048, AB_BLK * 128, 1024), id_dvk, (k ? 1u : acc));
+        }
+#pragma unroll
+        for (int k = 0; k < AB_BLK / 16; ++k)
+          umma_bf16_ss(tmem_base + TC_DQ, umma_smem_desc(aDS + k * 2048, AB_BLK * 128, 1024),
+                       umma_smem_desc(aK + k * 2048, AB_BLK * 128, 1024), id_dq, k ? 1u : 0u);
+        umma_commit(&qdo_empty[st]);
+        umma_commit(dq_full);
+        it_ph ^= 1;
+        if (++st == 2) { st = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    // ================================ compute warps ===============================
+    const int wg = (warp - 2) >> 2;      // which 64-query half of the block this thread covers
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;   // key row (S^T, dP^T, dV, dK) / query row (dQ)
+    const int krow = k0 + r;
+    const uint32_t t_lane = static_cast<uint32_t>(quarter * 32) << 16;
+    const int tid = threadIdx.x - 64;    // 0..255
+    uint32_t it_ph = 0;
+    for (int i = i_begin; i < nblk; ++i) {
+      const int q0 = i * AB_BLK;
+      // stage LSE (times log2e) and D for the 128 queries of this block
+      if (tid < AB_BLK) {
+        const int q = q0 + tid;
+        sLSE[tid] = (q < p.T) ? p.lse[static_cast<size_t>(bh) * p.T + q] * 1.4426950408889634f : 0.f;
+      } else {
+        const int q = q0 + tid - AB_BLK;
+        sD[tid - AB_BLK] = (q < p.T) ? p.D[static_cast<size_t>(bh) * p.T + q] : 0.f;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(sdp_full, it_ph);
+      tc_fence_after();
+      const bool edge = (k0 + AB_BLK > p.T) || (q0 + AB_BLK > p.T) || (p.causal && i == jb);
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        const int col0 = wg * 64 + c * 32;
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + col0, vs);
+        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + col0, vd);
+        tmem_ld_wait();
+        float pt[32], ds[32];
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          const int qi = col0 + e;
+          float pv = exp2f(__uint_as_float(vs[e]) * p.scale_log2 - sLSE[qi]);
+          float dp = __uint_as_float(vd[e]);
+          if (edge) {
+            const int q = q0 + qi;
+            if (krow >= p.T || q >= p.T || (p.causal && krow > q)) pv = 0.f;
+          }
+          float pd = pv;
+          if (p.drop_threshold) {
+            const uint64_t idx =
+                (static_cast<uint64_t>(bh) * p.T + (q0 + qi)) * static_cast<uint64_t>(p.T) + krow;
+            const bool keep = dropout_keep(p.drop_seed, idx, p.drop_threshold);
+            pd = keep ? pv * p.drop_scale : 0.f;
+            dp = keep ? dp * p.drop_scale : 0.f;
+          }
+          pt[e] = pd;
+          ds[e] = pv * (dp - sD[qi]) * p.scale;
+        }
+        uint8_t* rowP = sP + wg * (AB_BLK * 128) + r * 128;
+        uint8_t* rowS = sDS + wg * (AB_BLK * 128) + r * 128;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int chunk = (c * 4 + g) ^ (r & 7);
+          uint4 u;
+          u.x = pack_bf16x2(pt[g * 8 + 0], pt[g * 8 + 1]);
+          u.y = pack_bf16x2(pt[g * 8 + 2], pt[g * 8 + 3]);
+          u.z = pack_bf16x2(pt[g * 8 + 4], pt[g * 8 + 5]);
+          u.w = pack_bf16x2(pt[g * 8 + 6], pt[g * 8 + 7]);
+          *reinterpret_cast<uint4*>(rowP + chunk * 16) = u;
+          u.x = pack_bf16x2(ds[g * 8 + 0], ds[g * 8 + 1]);
+          u.y = pack_bf16x2(ds[g * 8 + 2], ds[g * 8 + 3]);
+          u.z = pack_bf16x2(ds[g * 8 + 4], ds[g * 8 + 5]);
+          u.w = pack_bf16x2(ds[g * 8 + 6], ds[g * 8 + 7]);
+          *reinterpret_cast<uint4*>(rowS + chunk * 16) = u;
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(pds_full);
+      // ---- drain dQ_i: rows = queries, this thread takes 32 of the 64 head-dim columns ----
+      mbar_wait(dq_full, it_ph);
+      tc_fence_after();
+      {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DQ + wg * 32, v);
+        tmem_ld_wait();
+        const int q = q0 + r;
+        if (q < p.T) {
+          float* dst = p.dq_acc + static_cast<size_t>(row_base + q) * p.d + h * AB_HD + wg * 32;
+#pragma unroll
+          for (int e = 0; e < 32; e += 4)
+            red_add_v4(dst + e, __uint_as_float(v[e]), __uint_as_float(v[e + 1]),
+                       __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(dq_empty);
+      it_ph ^= 1;
+    }
+    // ---- epilogue: dV (warpgroup 0) and dK (warpgroup 1), rows = keys ------------------------
+    // The last dq_full wait above also covers the final dV / dK MMAs (same commit).
+    if (i_begin < nblk) {
+      const uint32_t tcol = (wg == 0) ? TC_DV : TC_DK;
+      const bool ok = krow < p.T;   // tcgen05.ld is warp-collective: only the stores are predicated
+      __nv_bfloat16* dst = p.dqkv + static_cast<size_t>(row_base + (ok ? krow : k0)) * 3 * p.d +
+                           (wg == 0 ? 2 * p.d : p.d) + h * AB_HD;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + t_lane + tcol + c * 32, v);
+        tmem_ld_wait();
+        if (ok) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 u;
+            u.x = pack_bf16x2(__uint_as_float(v[g * 8 + 0]), __uint_as_float(v[g * 8 + 1]));
+            u.y = pack_bf16x2(__uint_as_float(v[g * 8 + 2]), __uint_as_float(v[g * 8 + 3]));
+            u.z = pack_bf16x2(__uint_as_float(v[g * 8 + 4]), __uint_as_float(v[g * 8 + 5]));
+            u.w = pack_bf16x2(__uint_as_float(v[g * 8 + 6]), __uint_as_float(v[g * 8 + 7]));
+            *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) = u;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// D[b,h,t] = sum_c dO[b,t,h,c] * O[b,t,h,c]   (one warp per (row, head))
+__global__ void __launch_bounds__(256)
+attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ O, const __nv_bfloat16* __restrict__ dO,
+                     float* __restrict__ D, int B, int T, int H) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw >= B * T * H) return;
+  const int m = gw / H, h = gw % H;
+  const size_t off = static_cast<size_t>(m) * H * AB_HD + h * AB_HD + lane * 2;
+  const float2 o = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(O + off));
+  const float2 g = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dO + off));
+  float s = o.x * g.x + o.y * g.y;
+#pragma unroll
+  for (int k = 16; k > 0; k >>= 1) s += __shfl_xor_sync(0xffffffffu, s, k);
+  if (lane == 0) {
+    const int b = m / T, t = m % T;
+    D[(static_cast<size_t>(b) * H + h) * T + t] = s;
+  }
+}
+
+// dq_acc fp32 [M, d] -> bf16 into dqkv[:, 0:d] (row stride 3d)
+__global__ void __launch_bounds__(256)
+attn_bwd_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int M,
+                           int d) {
+  const int nvec = d >> 3;
+  const size_t total = static_cast<size_t>(M) * nvec;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t m = i / nvec;
+    const int c = static_cast<int>(i % nvec);
+    const float4 a = reinterpret_cast<const float4*>(acc + m * d)[2 * c];
+    const float4 bq = reinterpret_cast<const float4*>(acc + m * d)[2 * c + 1];
+    uint4 u;
+    u.x = pack_bf16x2(a.x, a.y);
+    u.y = pack_bf16x2(a.z, a.w);
+    u.z = pack_bf16x2(bq.x, bq.y);
+    u.w = pack_bf16x2(bq.z, bq.w);
+    reinterpret_cast<uint4*>(dqkv + m * 3 * d)[c] = u;
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* dout,
+                                  const float* lse, void* dqkv, float* D, float* dq_acc, int B,
+                                  int T, int H, int head_dim, int causal, float drop_p,
+                                  unsigned int seed, void* stream) {
+  if (head_dim != AB_HD) return -5;
+  const int d = H * head_dim;
+  const int M = B * T;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  CUtensorMap map_qkv, map_do;
+  int rc = make_tmap_2d_bf16(&map_qkv, qkv, M, 3 * d, 3 * d, AB_BLK, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&map_do, dout, M, d, d, AB_BLK, 64);
+  if (rc) return rc;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_done[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_done[dev & 63] = true;
+  }
+  cudaMemsetAsync(dq_acc, 0, static_cast<size_t>(M) * d * sizeof(float), s);
+  {
+    const long warps = static_cast<long>(M) * H;
+    const int blocks = static_cast<int>((warps * 32 + 255) / 256);
+    attn_bwd_prep_kernel<<<blocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(out),
+                                                static_cast<const __nv_bfloat16*>(dout), D, B, T, H);
+  }
+  AttnBwdParams p;
+  p.lse = lse;
+  p.D = D;
+  p.dq_acc = dq_acc;
+  p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
+  p.B = B;
+  p.T = T;
+  p.H = H;
+  p.d = d;
+  p.scale = 1.f / sqrtf(static_cast<float>(head_dim));
+  p.scale_log2 = p.scale * 1.4426950408889634f;
+  p.causal = causal;
+  if (drop_p > 0.f && drop_p < 1.f) {
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
+    p.drop_scale = 1.f / (1.f - drop_p);
+  } else {
+    p.drop_threshold = 0;
+    p.drop_scale = 1.f;
+  }
+  p.drop_seed = seed;
+  const int grid = B * H * ((T + AB_BLK - 1) / AB_BLK);
+  attn_bwd_kernel<<<grid, AB_THREADS, AB_SMEM, s>>>(map_qkv, map_do, p);
+  {
+    const size_t work = static_cast<size_t>(M) * (d / 8);
+    size_t blocks = (work + 255) / 256;
+    const size_t cap = static_cast<size_t>(device_sm_count()) * 8;
+    if (blocks > cap) blocks = cap;
+    attn_bwd_dq_convert_kernel<<<static_cast<int>(blocks), 256, 0, s>>>(
+        dq_acc, static_cast<__nv_bfloat16*>(dqkv), M, d);
+  }
+  return static_cast<int>(cudaGetLastError());
+}

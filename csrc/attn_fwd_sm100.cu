@@ -1,0 +1,379 @@
+// Fused attention forward for sm_100a: S = Q K^T and O = P V on tcgen05 tensor cores with the
+// accumulators in tensor memory, online softmax in registers, K/V streamed by TMA.  The T x T score
+// matrix is never written to memory.
+//
+// Replaces the reference's unfused math path (benchmarking/train_harness.py:127 ->
+// nn.MultiheadAttention with need_weights=True: bmm, fp32 softmax, dropout, bmm and a discarded
+// head-mean).  Non-causal by default because the reference passes no mask
+// (SURVEY Q5); `causal` switches the mask on.  Dropout is applied to P after the softmax with a
+// counter-based RNG keyed on (seed, b, h, q, k) so that backward regenerates the same mask.
+//
+// Input  qkv [B*T, 3*d]  bf16, row m = b*T + t, columns [q | k | v], head h at h*64 inside each.
+// Output out [B*T, d]    bf16, head h at columns h*64 .. h*64+63;   lse [B*H, T] fp32 (natural log).
+//
+// CTA = one (batch, head, 128-row query block), 320 threads:
+//   warp 0      TMA producer: Q once, then K/V tiles of 128 keys through 3-stage rings
+//   warp 1      MMA issuer:   S[w] = Q K_j^T  (M128 N128 K64),  O_blk[w] = P[w] V_j  (M128 N64 K128)
+//   warps 2-5   softmax warpgroup 0 : even key blocks      (thread = one query row)
+//   warps 6-9   softmax warpgroup 1 : odd key blocks
+// Each warpgroup owns one S buffer (128 TMEM columns), one O_blk buffer (64 columns) and one P
+// buffer in shared memory (bf16, 128B-swizzled K-major so it is directly the A operand of P V), and
+// keeps its own running (max, sum, O) in registers; the two partial results are merged at the end.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b200_internal.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int AT_BM = 128;       // query rows per CTA
+constexpr int AT_BN = 128;       // keys per block
+constexpr int AT_HD = 64;        // head dim
+constexpr int AT_KV_STAGES = 3;
+constexpr int AT_THREADS = 320;
+constexpr int AT_TILE = AT_BN * AT_HD * 2;   // 16 KiB: one [128 x 64] bf16 tile
+constexpr int AT_PBYTES = AT_BM * AT_BN * 2; // 32 KiB: one P buffer
+constexpr int AT_SMEM = AT_TILE * (1 + 2 * AT_KV_STAGES) + 2 * AT_PBYTES + 1024 /*bars+merge*/ +
+                        1024 /*align*/;
+constexpr float NEG_BIG = -1.0e30f;
+
+struct AttnFwdParams {
+  __nv_bfloat16* out;
+  float* lse;
+  int B, T, H, d;
+  float scale_log2;       // softmax_scale * log2(e)
+  int causal;
+  uint32_t drop_threshold;
+  float drop_scale;
+  uint32_t drop_seed;
+};
+
+__device__ __forceinline__ uint64_t attn_drop_index(int bh, int q, int k, int T) {
+  return (static_cast<uint64_t>(bh) * T + q) * static_cast<uint64_t>(T) + k;
+}
+
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + AT_TILE;
+  uint8_t* sV = sK + AT_KV_STAGES * AT_TILE;
+  uint8_t* sP = sV + AT_KV_STAGES * AT_TILE;  // 2 x 32 KiB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * AT_PBYTES);
+  uint64_t* q_full = bars;                         // 1
+  uint64_t* k_full = bars + 1;                     // [3]
+  uint64_t* k_empty = bars + 4;                    // [3]
+  uint64_t* v_full = bars + 7;                     // [3]
+  uint64_t* v_empty = bars + 10;                   // [3]
+  uint64_t* s_full = bars + 13;                    // [2]
+  uint64_t* p_full = bars + 15;                    // [2]
+  uint64_t* o_full = bars + 17;                    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
+  float* merge_ml = reinterpret_cast<float*>(bars + 20);  // [2][128] m, l of warpgroup 1
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qblocks = (p.T + AT_BM - 1) / AT_BM;
+  const int qb = blockIdx.x % qblocks;
+  const int bh = blockIdx.x / qblocks;
+  const int b = bh / p.H, h = bh % p.H;
+  const int q0 = qb * AT_BM;
+  const int row_base = b * p.T;  // first row of this batch element in qkv
+  int nkv = (p.T + AT_BN - 1) / AT_BN;
+  if (p.causal) nkv = min(nkv, qb + 1);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_qkv);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < AT_KV_STAGES; ++s) {
+      mbar_init(&k_full[s], 1);
+      mbar_init(&k_empty[s], 1);
+      mbar_init(&v_full[s], 1);
+      mbar_init(&v_empty[s], 1);
+    }
+    for (int w = 0; w < 2; ++w) {
+      mbar_init(&s_full[w], 1);
+      mbar_init(&p_full[w], 128);
+      mbar_init(&o_full[w], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384)
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      const int qcol = h * AT_HD, kcol = p.d + h * AT_HD, vcol = 2 * p.d + h * AT_HD;
+      mbar_expect_tx(q_full, AT_TILE);
+      tma_load_2d(&map_qkv, q_full, sQ, qcol, row_base + q0);
+      int ks = 0, vs = 0;
+      uint32_t kph = 0, vph = 0;
+      auto load_k = [&](int j) {
+        mbar_wait(&k_empty[ks], kph ^ 1);
+        mbar_expect_tx(&k_full[ks], AT_TILE);
+        tma_load_2d(&map_qkv, &k_full[ks], sK + ks * AT_TILE, kcol, row_base + j * AT_BN);
+        if (++ks == AT_KV_STAGES) { ks = 0; kph ^= 1; }
+      };
+      auto load_v = [&](int j) {
+        mbar_wait(&v_empty[vs], vph ^ 1);
+        mbar_expect_tx(&v_full[vs], AT_TILE);
+        tma_load_2d(&map_qkv, &v_full[vs], sV + vs * AT_TILE, vcol, row_base + j * AT_BN);
+        if (++vs == AT_KV_STAGES) { vs = 0; vph ^= 1; }
+      };
+      load_k(0);
+      if (nkv > 1) load_k(1);
+      for (int j = 0; j < nkv; ++j) {
+        load_v(j);
+        if (j + 2 < nkv) load_k(j + 2);
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      const uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN, false, false);
+      const uint32_t idesc_o = umma_idesc_bf16(AT_BM, AT_HD, false, true);
+      const uint32_t aQ = smem_u32(sQ);
+      int ks = 0, vs = 0;
+      uint32_t kph = 0, vph = 0;
+      auto issue_s = [&](int w) {
+        mbar_wait(&k_full[ks], kph);
+        tc_fence_after();
+        const uint32_t aK = smem_u32(sK + ks * AT_TILE);
+#pragma unroll
+        for (int k = 0; k < AT_HD / 16; ++k)
+          umma_bf16_ss(tmem_base + w * 128, umma_smem_desc(aQ + k * 32, 16, 1024),
+                       umma_smem_desc(aK + k * 32, 16, 1024), idesc_s, k ? 1u : 0u);
+        umma_commit(&k_empty[ks]);
+        umma_commit(&s_full[w]);
+        if (++ks == AT_KV_STAGES) { ks = 0; kph ^= 1; }
+      };
+      mbar_wait(q_full, 0);
+      tc_fence_after();
+      issue_s(0);
+      if (nkv > 1) issue_s(1);
+      uint32_t pph[2] = {0, 0};
+      for (int j = 0; j < nkv; ++j) {
+        const int w = j & 1;
+        mbar_wait(&p_full[w], pph[w]);  // P(j) in smem, S[w] fully read
+        pph[w] ^= 1;
+        tc_fence_after();
+        if (j + 2 < nkv) issue_s(w);    // next scores for this warpgroup first
+        mbar_wait(&v_full[vs], vph);
+        tc_fence_after();
+        const uint32_t aP = smem_u32(sP + w * AT_PBYTES);
+        const uint32_t aV = smem_u32(sV + vs * AT_TILE);
+#pragma unroll
+        for (int k = 0; k < AT_BN / 16; ++k)
+          umma_bf16_ss(tmem_base + 256 + w * 64,
+                       umma_smem_desc(aP + (k >> 2) * (AT_BM * 128) + (k & 3) * 32, 16, 1024),
+                       umma_smem_desc(aV + k * 2048, AT_BN * 128, 1024), idesc_o, k ? 1u : 0u);
+        umma_commit(&v_empty[vs]);
+        umma_commit(&o_full[w]);
+        if (++vs == AT_KV_STAGES) { vs = 0; vph ^= 1; }
+      }
+    }
+  } else {
+    // ================================ softmax warpgroups ==========================
+    const int w = (warp - 2) >> 2;        // warpgroup 0 / 1
+    const int quarter = warp & 3;         // TMEM lane quarter
+    const int r = quarter * 32 + lane;    // query row inside the block
+    const int qrow = q0 + r;
+    const uint32_t t_lane = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t tS = tmem_base + t_lane + w * 128;
+    const uint32_t tO = tmem_base + t_lane + 256 + w * 64;
+    uint8_t* myP = sP + w * AT_PBYTES + r * 128;
+
+    float o[AT_HD];
+#pragma unroll
+    for (int i = 0; i < AT_HD; ++i) o[i] = 0.f;
+    float m_run = NEG_BIG, l_run = 0.f, m_ref = NEG_BIG, m_prev = NEG_BIG;
+    uint32_t sph = 0, oph = 0;
+    int n_done = 0;
+
+    auto accumulate_prev = [&]() {
+      // O_blk of this warpgroup's previous block is relative to m_prev; o[] is relative to m_ref.
+      mbar_wait(&o_full[w], oph);
+      oph ^= 1;
+      tc_fence_after();
+      const float alpha = exp2f(m_ref - m_prev);
+#pragma unroll
+      for (int c = 0; c < AT_HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tO + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      }
+      m_ref = m_prev;
+    };
+
+    for (int j = w; j < nkv; j += 2) {
+      mbar_wait(&s_full[w], sph);
+      sph ^= 1;
+      tc_fence_after();
+      const int k0 = j * AT_BN;
+      const bool need_mask = (k0 + AT_BN > p.T) || (p.causal && j == qb);
+      // ---- pass 1: row maximum -------------------------------------------------------
+      float mx = NEG_BIG;
+#pragma unroll 1
+      for (int c = 0; c < AT_BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tS + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(v[i]);
+          if (need_mask) {
+            const int kk = k0 + c * 32 + i;
+            if (kk >= p.T || (p.causal && kk > qrow)) s = NEG_BIG;
+          }
+          mx = fmaxf(mx, s);
+        }
+      }
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      // previous block of this warpgroup: its P buffer must be free before we overwrite it
+      if (n_done > 0) accumulate_prev();
+      // ---- pass 2: P = exp2(s*scale - m_new), row sum, bf16 -> swizzled smem -----------
+      float rs = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < AT_BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tS + c * 32, v);
+        tmem_ld_wait();
+        float pv[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(v[i]);
+          float e = exp2f(s * p.scale_log2 - m_new);
+          if (need_mask) {
+            const int kk = k0 + c * 32 + i;
+            if (kk >= p.T || (p.causal && kk > qrow)) e = 0.f;
+          }
+          rs += e;
+          pv[i] = e;
+        }
+        if (p.drop_threshold) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const uint64_t idx = attn_drop_index(bh, qrow, k0 + c * 32 + i, p.T);
+            pv[i] = dropout_keep(p.drop_seed, idx, p.drop_threshold) ? pv[i] * p.drop_scale : 0.f;
+          }
+        }
+        // 32 keys = 4 x 16-byte chunks of the 128-byte swizzled row; chunk index XOR (row & 7)
+        uint8_t* dst = myP + (c >> 1) * (AT_BM * 128);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 u;
+          u.x = pack_bf16x2(pv[g * 8 + 0], pv[g * 8 + 1]);
+          u.y = pack_bf16x2(pv[g * 8 + 2], pv[g * 8 + 3]);
+          u.z = pack_bf16x2(pv[g * 8 + 4], pv[g * 8 + 5]);
+          u.w = pack_bf16x2(pv[g * 8 + 6], pv[g * 8 + 7]);
+          const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
+          *reinterpret_cast<uint4*>(dst + chunk * 16) = u;
+        }
+      }
+      l_run = l_run * exp2f(m_run - m_new) + rs;
+      m_run = m_new;
+      m_prev = m_new;
+      tc_fence_before();
+      fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core
+      mbar_arrive(&p_full[w]);
+      ++n_done;
+    }
+    if (n_done > 0) accumulate_prev();
+
+    // ---- merge the two warpgroups and write out -------------------------------------------
+    // warpgroup 1 parks (m, l, O) in shared memory (its own P buffer is idle by now).
+    float* park = reinterpret_cast<float*>(sP + AT_PBYTES);  // [64][128] fp32, column-major by row
+    if (w == 1) {
+      merge_ml[r] = m_ref;
+      merge_ml[128 + r] = l_run;
+#pragma unroll
+      for (int i = 0; i < AT_HD; ++i) park[i * 128 + r] = o[i];
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (w == 0) {
+      const float m1 = merge_ml[r], l1 = merge_ml[128 + r];
+      const float m = fmaxf(m_ref, m1);
+      const float a0 = exp2f(m_ref - m), a1 = exp2f(m1 - m);
+      const float l = l_run * a0 + l1 * a1;
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      if (qrow < p.T) {
+        __nv_bfloat16* dst = p.out + static_cast<size_t>(row_base + qrow) * p.d + h * AT_HD;
+#pragma unroll
+        for (int g = 0; g < AT_HD / 8; ++g) {
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            f[i] = (o[g * 8 + i] * a0 + park[(g * 8 + i) * 128 + r] * a1) * inv;
+          uint4 u;
+          u.x = pack_bf16x2(f[0], f[1]);
+          u.y = pack_bf16x2(f[2], f[3]);
+          u.z = pack_bf16x2(f[4], f[5]);
+          u.w = pack_bf16x2(f[6], f[7]);
+          *reinterpret_cast<uint4*>(dst + g * 8) = u;
+        }
+        p.lse[static_cast<size_t>(bh) * p.T + qrow] = (m + log2f(l)) * 0.6931471805599453f;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H,
+                                  int head_dim, int causal, float drop_p, unsigned int seed,
+                                  void* stream) {
+  if (head_dim != AT_HD) return -5;
+  const int d = H * head_dim;
+  CUtensorMap map;
+  int rc = make_tmap_2d_bf16(&map, qkv, static_cast<uint64_t>(B) * T, 3 * d, 3 * d, AT_BN, 64);
+  if (rc) return rc;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_done[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_done[dev & 63] = true;
+  }
+  AttnFwdParams p;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.lse = lse;
+  p.B = B;
+  p.T = T;
+  p.H = H;
+  p.d = d;
+  p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(head_dim));
+  p.causal = causal;
+  if (drop_p > 0.f && drop_p < 1.f) {
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
+    p.drop_scale = 1.f / (1.f - drop_p);
+  } else {
+    p.drop_threshold = 0;
+    p.drop_scale = 1.f;
+  }
+  p.drop_seed = seed;
+  const int grid = B * H * ((T + AT_BM - 1) / AT_BM);
+  attn_fwd_kernel<<<grid, AT_THREADS, AT_SMEM, static_cast<cudaStream_t>(stream)>>>(map, p);
+  return static_cast<int>(cudaGetLastError());
+}

@@ -11,6 +11,8 @@
 #ifndef B200BENCH_H_
 #define B200BENCH_H_
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -32,6 +34,63 @@ int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, i
                    int ldd, int a_mn, int b_mn, int epi, const void* bias, const void* aux,
                    void* D2, float drop_p, unsigned int drop_seed, int bn_hint, int max_ctas,
                    void* stream);
+
+/* ---- attention (TH:127) ------------------------------------------------------
+ * qkv [B*T, 3*H*hd] bf16 (columns q|k|v, head h at h*hd in each), out [B*T, H*hd] bf16,
+ * lse [B*H, T] fp32 (natural log).  head_dim must be 64.  causal=0 reproduces the reference
+ * (no mask).  drop_p > 0 drops attention probabilities after the softmax (counter-based RNG,
+ * the backward regenerates the mask from the same seed). */
+int b200_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int head_dim,
+                       int causal, float drop_p, unsigned int seed, void* stream);
+/* dqkv [B*T, 3*H*hd] bf16 receives dQ|dK|dV.  D [B*H, T] fp32 and dq_acc [B*T, H*hd] fp32 are
+ * caller-provided scratch (dq_acc is zeroed inside). */
+int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
+                       void* dqkv, float* D, float* dq_acc, int B, int T, int H, int head_dim,
+                       int causal, float drop_p, unsigned int seed, void* stream);
+
+/* ---- LayerNorm (TH:113,117,56) ------------------------------------------------ */
+int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
+                       float* rstd, int M, int d, float eps, void* stream);
+/* dx = LayerNorm'(dy) + dres (dres may be NULL) */
+int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                       const float* rstd, const void* dres, void* dx, int M, int d, void* stream);
+/* Scratch (fp32 partial sums) needed by the two column reductions below. */
+size_t b200_colreduce_scratch_bytes(int M, int N, int outputs);
+/* dgamma[n] (+)= sum_m dy*xhat, dbeta[n] (+)= sum_m dy.  scratch >= colreduce_scratch_bytes(M,d,2) */
+int b200_layernorm_bwd_params(const void* dy, const void* x, const float* mean, const float* rstd,
+                              void* dgamma, void* dbeta, int M, int d, int accumulate,
+                              void* scratch, size_t scratch_bytes, void* stream);
+/* out[n] (+)= sum_m dy[m,n]   (bias gradients).  scratch >= colreduce_scratch_bytes(M,N,1) */
+int b200_colsum(const void* dy, void* out, int M, int N, int ld, int accumulate, void* scratch,
+                size_t scratch_bytes, void* stream);
+
+/* ---- embedding (TH:85-89) ------------------------------------------------------ */
+int b200_embedding_fwd(const int* tokens, const void* wte, const void* wpe, void* out, int B,
+                       int T, int d, float drop_p, unsigned int seed, void* stream);
+/* dwte[tok] += dx (atomic, lands on top of the tied lm_head wgrad), dwpe[t] (+)= sum_b dx */
+int b200_embedding_bwd(const int* tokens, const void* dx, void* dwte, void* dwpe, int B, int T,
+                       int d, float drop_p, unsigned int seed, int accumulate_wpe, void* stream);
+
+/* ---- softmax cross-entropy forward+backward (TH:99-103) --------------------------
+ * logits [M, ld] bf16 are overwritten by dlogits * grad_scale / n_valid when write_grad != 0.
+ * loss_out (device scalar) = mean over rows with target != ignore_index, times loss_scale. */
+int b200_cross_entropy(void* logits, const int* targets, float* loss_rows, int* n_valid,
+                       float* loss_out, int M, int V, int ld, int ignore_index, float grad_scale,
+                       int write_grad, int accumulate_loss, float loss_scale, void* stream);
+
+/* ---- optimizer (TH:329, configs/deepspeed/zero2.json:2,27-44) -------------------
+ * hp: 9 floats on the device {lr, beta1, beta2, eps, wd, 1/bc1, 1/sqrt(bc2), grad_scale, clip}.
+ * gnorm_sq (nullable): squared global grad norm for clipping. n % 8 == 0. */
+int b200_adamw_set_hp(float* hp, float lr, float beta1, float beta2, float eps, float wd,
+                      float inv_bias_corr1, float inv_sqrt_bias_corr2, float grad_scale,
+                      float clip_norm, void* stream);
+int b200_adamw(float* master, float* m, float* v, const void* grad, void* w_out, size_t n,
+               const float* hp, const float* gnorm_sq, void* stream);
+/* *out += scale^2 * sum(grad^2) */
+int b200_sumsq(const void* grad, size_t n, float scale, float* out, void* stream);
+/* out = dropout_mask(seed) * in / (1-p): re-applies the mask a GEMM epilogue drew (same indexing) */
+int b200_dropout_apply(const void* in, void* out, int M, int N, float drop_p, unsigned int seed,
+                       void* stream);
 
 #ifdef __cplusplus
 }
