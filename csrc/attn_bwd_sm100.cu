@@ -48,6 +48,7 @@ struct AttnBwdParams {
   uint32_t drop_threshold;
   float drop_scale;
   uint32_t drop_seed;
+  const uint32_t* seed_ptr;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -180,6 +181,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
   } else {
     // ================================ compute warps ===============================
     const int wg = (warp - 2) >> 2;      // which 64-query half of the block this thread covers
+    const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;   // key row (S^T, dP^T, dV, dK) / query row (dQ)
     const int krow = k0 + r;
@@ -221,7 +223,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
           if (p.drop_threshold) {
             const uint64_t idx =
                 (static_cast<uint64_t>(bh) * p.T + (q0 + qi)) * static_cast<uint64_t>(p.T) + krow;
-            const bool keep = dropout_keep(p.drop_seed, idx, p.drop_threshold);
+            const bool keep = dropout_keep(seed, idx, p.drop_threshold);
             pd = keep ? pv * p.drop_scale : 0.f;
             dp = keep ? dp * p.drop_scale : 0.f;
           }
@@ -398,6 +400,7 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
     p.drop_scale = 1.f;
   }
   p.drop_seed = seed;
+  p.seed_ptr = step_seed_ptr();
   const int grid = B * H * ((T + AB_BLK - 1) / AB_BLK);
   attn_bwd_kernel<<<grid, AB_THREADS, AB_SMEM, s>>>(map_qkv, map_do, p);
   {

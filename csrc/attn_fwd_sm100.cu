@@ -49,6 +49,7 @@ struct AttnFwdParams {
   uint32_t drop_threshold;
   float drop_scale;
   uint32_t drop_seed;
+  const uint32_t* seed_ptr;
 };
 
 __device__ __forceinline__ uint64_t attn_drop_index(int bh, int q, int k, int T) {
@@ -184,6 +185,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
   } else {
     // ================================ softmax warpgroups ==========================
     const int w = (warp - 2) >> 2;        // warpgroup 0 / 1
+    const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
     const int quarter = warp & 3;         // TMEM lane quarter
     const int r = quarter * 32 + lane;    // query row inside the block
     const int qrow = q0 + r;
@@ -265,7 +267,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const uint64_t idx = attn_drop_index(bh, qrow, k0 + c * 32 + i, p.T);
-            pv[i] = dropout_keep(p.drop_seed, idx, p.drop_threshold) ? pv[i] * p.drop_scale : 0.f;
+            pv[i] = dropout_keep(seed, idx, p.drop_threshold) ? pv[i] * p.drop_scale : 0.f;
           }
         }
         // 32 keys = 4 x 16-byte chunks of the 128-byte swizzled row; chunk index XOR (row & 7)
@@ -373,6 +375,7 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B,
     p.drop_scale = 1.f;
   }
   p.drop_seed = seed;
+  p.seed_ptr = step_seed_ptr();
   const int grid = B * H * ((T + AT_BM - 1) / AT_BM);
   attn_fwd_kernel<<<grid, AT_THREADS, AT_SMEM, static_cast<cudaStream_t>(stream)>>>(map, p);
   return static_cast<int>(cudaGetLastError());

@@ -253,7 +253,8 @@ __global__ void colreduce_stage2_kernel(const float* __restrict__ scratch, int R
 __global__ void __launch_bounds__(256)
 embedding_fwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restrict__ wte,
                      const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out, int M,
-                     int T, int d, uint32_t thr, float scale, uint32_t seed) {
+                     int T, int d, uint32_t thr, float scale, uint32_t seed, const uint32_t* __restrict__ seed_ptr) {
+  if (thr && seed_ptr) seed ^= __ldg(seed_ptr);
   const int nvec = d >> 3;
   const size_t total = static_cast<size_t>(M) * nvec;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
@@ -281,7 +282,9 @@ embedding_fwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restric
 __global__ void __launch_bounds__(256)
 embedding_bwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restrict__ dx,
                      __nv_bfloat16* __restrict__ dwte, __nv_bfloat16* __restrict__ dwpe, int B, int T,
-                     int d, uint32_t thr, float scale, uint32_t seed, int accumulate_wpe) {
+                     int d, uint32_t thr, float scale, uint32_t seed, int accumulate_wpe,
+                     const uint32_t* __restrict__ seed_ptr) {
+  if (thr && seed_ptr) seed ^= __ldg(seed_ptr);
   const int nvec = d >> 3;
   const size_t total = static_cast<size_t>(T) * nvec;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
@@ -545,7 +548,9 @@ sumsq_kernel(const __nv_bfloat16* __restrict__ g, size_t n, float scale, float* 
 
 __global__ void __launch_bounds__(256)
 dropout_apply_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int M,
-                     int N, uint32_t thr, float scale, uint32_t seed) {
+                     int N, uint32_t thr, float scale, uint32_t seed,
+                     const uint32_t* __restrict__ seed_ptr) {
+  if (seed_ptr) seed ^= __ldg(seed_ptr);
   const int nvec = N >> 3;
   const size_t total = static_cast<size_t>(M) * nvec;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
@@ -568,6 +573,11 @@ __global__ void fill_adam_hp_kernel(float* hp, float lr, float b1, float b2, flo
   hp[0] = lr; hp[1] = b1; hp[2] = b2; hp[3] = eps; hp[4] = wd;
   hp[5] = ibc1; hp[6] = isbc2; hp[7] = gscale; hp[8] = clip;
 }
+
+static const uint32_t* g_step_seed_ptr = nullptr;
+const uint32_t* step_seed_ptr() { return g_step_seed_ptr; }
+
+__global__ void bump_step_seed_kernel(uint32_t* w) { *w = *w * 1664525u + 1013904223u; }
 
 static inline uint32_t drop_thr(float p) {
   if (!(p > 0.f) || p >= 1.f) return 0;
@@ -675,7 +685,7 @@ extern "C" int b200_embedding_fwd(const int* tokens, const void* wte, const void
   const float scale = drop_p > 0.f && drop_p < 1.f ? 1.f / (1.f - drop_p) : 1.f;
   embedding_fwd_kernel<<<grid_for(work, 256, 8), 256, 0, s>>>(
       tokens, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
-      static_cast<__nv_bfloat16*>(out), B * T, T, d, drop_thr(drop_p), scale, seed);
+      static_cast<__nv_bfloat16*>(out), B * T, T, d, drop_thr(drop_p), scale, seed, step_seed_ptr());
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -688,7 +698,8 @@ extern "C" int b200_embedding_bwd(const int* tokens, const void* dx, void* dwte,
   const float scale = drop_p > 0.f && drop_p < 1.f ? 1.f / (1.f - drop_p) : 1.f;
   embedding_bwd_kernel<<<grid_for(work, 256, 8), 256, 0, s>>>(
       tokens, static_cast<const __nv_bfloat16*>(dx), static_cast<__nv_bfloat16*>(dwte),
-      static_cast<__nv_bfloat16*>(dwpe), B, T, d, drop_thr(drop_p), scale, seed, accumulate_wpe);
+      static_cast<__nv_bfloat16*>(dwpe), B, T, d, drop_thr(drop_p), scale, seed, accumulate_wpe,
+      step_seed_ptr());
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -747,6 +758,20 @@ extern "C" int b200_dropout_apply(const void* in, void* out, int M, int N, float
   const size_t work = static_cast<size_t>(M) * (N / 8);
   dropout_apply_kernel<<<grid_for(work, 256, 8), 256, 0, s>>>(
       static_cast<const __nv_bfloat16*>(in), static_cast<__nv_bfloat16*>(out), M, N, thr,
-      1.f / (1.f - drop_p), seed);
+      1.f / (1.f - drop_p), seed, step_seed_ptr());
+  return static_cast<int>(cudaGetLastError());
+}
+
+// Registers a device word that every dropout site XORs into its seed, and advances it.  The engine
+// captures b200_step_seed_advance at the head of its micro-step graph, so each replay draws new
+// masks while forward and backward of the same micro-step still agree.
+extern "C" int b200_step_seed_register(unsigned int* device_word) {
+  g_step_seed_ptr = device_word;
+  return 0;
+}
+extern "C" int b200_step_seed_advance(void* stream) {
+  if (!g_step_seed_ptr) return -6;
+  bump_step_seed_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(
+      const_cast<uint32_t*>(g_step_seed_ptr));
   return static_cast<int>(cudaGetLastError());
 }

@@ -55,6 +55,7 @@ struct GemmParams {
   float drop_scale;             // 1/(1-p)
   uint32_t drop_threshold;      // p * 2^32, 0 = no dropout
   uint32_t drop_seed;
+  const uint32_t* seed_ptr;     // per-step seed word in device memory (nullable)
   int num_m_tiles, num_n_tiles;
 };
 
@@ -181,6 +182,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   } else {
     // ================================ epilogue ====================================
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -240,7 +242,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                   const uint64_t idx = static_cast<uint64_t>(row) * p.N + (col + j);
-                  v[j] = dropout_keep(p.drop_seed, idx, p.drop_threshold) ? v[j] * p.drop_scale
+                  v[j] = dropout_keep(seed, idx, p.drop_threshold) ? v[j] * p.drop_scale
                                                                           : 0.0f;
                 }
               }
@@ -426,6 +428,7 @@ extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int 
     p.drop_threshold = 0;
   }
   p.drop_seed = drop_seed;
+  p.seed_ptr = step_seed_ptr();
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (BN == 256) return launch_gemm<256>(ma, mb, p, max_ctas, s);
   return launch_gemm<128>(ma, mb, p, max_ctas, s);

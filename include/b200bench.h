@@ -92,6 +92,11 @@ int b200_sumsq(const void* grad, size_t n, float scale, float* out, void* stream
 int b200_dropout_apply(const void* in, void* out, int M, int N, float drop_p, unsigned int seed,
                        void* stream);
 
+/* Per-step dropout seed: a device word XORed into every dropout seed.  Register once, then launch
+ * b200_step_seed_advance at the start of each micro-step (capturable in a CUDA graph). */
+int b200_step_seed_register(unsigned int* device_word);
+int b200_step_seed_advance(void* stream);
+
 #ifdef __cplusplus
 }
 #endif
