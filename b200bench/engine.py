@@ -120,7 +120,7 @@ class NativeEngine:
         self.attD = e(self.B * self.H * self.T, dt=torch.float32)
         sbytes = max(self.ops.colreduce_scratch_bytes(M, 4 * d, 1), self.ops.colreduce_scratch_bytes(M, d, 2),
                      self.ops.colreduce_scratch_bytes(M, 3 * d, 1))
-        self.scratch = torch.empty(sbytes // 4 + 64, dtype=torch.float32, device=dev)
+        self.scratch = torch.zeros(sbytes // 4 + 64, dtype=torch.float32, device=dev)   # counters start at 0
         self.seed_base = seed
         self.step_seed = torch.full((1,), seed, dtype=torch.int32, device=dev)
         self.ops.step_seed_register(self.step_seed)

@@ -148,13 +148,13 @@ class NativeOps:
                                                     M, d, int(accumulate), _p(scratch),
                                                     scratch.numel() * scratch.element_size(), _stream()),
                  "layernorm_bwd_params")
-        self.launches += 2
+        self.launches += 1
 
     def colsum(self, dy, out, scratch, accumulate=False, ld=None) -> None:
         M, N = dy.shape
         self._ck(self.lib.b200_colsum(_p(dy), _p(out), M, N, ld or N, int(accumulate), _p(scratch),
                                       scratch.numel() * scratch.element_size(), _stream()), "colsum")
-        self.launches += 2
+        self.launches += 1
 
     # ---- embedding / loss -----------------------------------------------------------------------
     def embedding_fwd(self, tokens, wte, wpe, out, B, T, d, drop_p=0.0, seed=0) -> None:

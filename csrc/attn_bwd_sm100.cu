@@ -17,12 +17,15 @@
 // dQ_i is added to an fp32 accumulator in global memory (vector red.add) because every key block
 // contributes to it; a small kernel converts it to bf16 afterwards.
 //
-// 320 threads: warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 compute (two threads per key
-// row, each covering 64 of the 128 query columns).
+// 384 threads: warpgroup 0 = TMA producer (warp 0) + MMA issuer (warp 1), warpgroups 1-2 = compute
+// (two threads per key row, each covering 64 of the 128 query columns); registers re-balanced
+// with setmaxnreg (40 / 232).
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include <type_traits>
 
 #include "b200_internal.h"
 #include "sm100_ptx.cuh"
@@ -31,11 +34,11 @@ namespace b200 {
 
 constexpr int AB_BLK = 128;
 constexpr int AB_HD = 64;
-constexpr int AB_THREADS = 320;
+constexpr int AB_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps), warpgroups 1-2: compute
 constexpr int AB_TILE = AB_BLK * AB_HD * 2;    // 16 KiB
 constexpr int AB_PBYTES = AB_BLK * AB_BLK * 2; // 32 KiB
 constexpr int AB_SMEM = 2 * AB_TILE /*K,V*/ + 4 * AB_TILE /*Q,dO x2*/ + 2 * AB_PBYTES /*P,dS*/ +
-                        2 * AB_BLK * 4 /*lse,D*/ + 256 /*bars*/ + 1024 /*align*/;
+                        3 * AB_BLK * 4 /*lse,D,keys*/ + 256 /*bars*/ + 1024 /*align*/;
 
 struct AttnBwdParams {
   const float* lse;
@@ -71,7 +74,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
   uint8_t* sDS = sP + AB_PBYTES;         // dS^T same layout
   float* sLSE = reinterpret_cast<float*>(sDS + AB_PBYTES);  // [128] (already times log2e)
   float* sD = sLSE + AB_BLK;                                 // [128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sD + AB_BLK);
+  uint32_t* sKey = reinterpret_cast<uint32_t*>(sD + AB_BLK); // [128] dropout row keys
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKey + AB_BLK);
   uint64_t* kv_full = bars;          // 1
   uint64_t* qdo_full = bars + 1;     // [2]
   uint64_t* qdo_empty = bars + 3;    // [2]
@@ -111,6 +115,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
   const uint32_t tmem_base = *tmem_slot;
   constexpr uint32_t TC_S = 0, TC_DP = 128, TC_DV = 256, TC_DK = 320, TC_DQ = 384;
 
+  if (warp < 4) {
+    setmaxnreg_dec<40>();
   if (warp == 0) {
     // ================================ TMA producer ================================
     if (lane == 0) {
@@ -178,60 +184,79 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
         if (++st == 2) { st = 0; ph ^= 1; }
       }
     }
+  }
   } else {
+    setmaxnreg_inc<232>();
     // ================================ compute warps ===============================
-    const int wg = (warp - 2) >> 2;      // which 64-query half of the block this thread covers
+    const int wg = (warp - 4) >> 2;      // which 64-query half of the block this thread covers
     const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;   // key row (S^T, dP^T, dV, dK) / query row (dQ)
     const int krow = k0 + r;
     const uint32_t t_lane = static_cast<uint32_t>(quarter * 32) << 16;
-    const int tid = threadIdx.x - 64;    // 0..255
+    const int tid = threadIdx.x - 128;   // 0..255
+    const bool drop = p.drop_threshold != 0;
+    const uint32_t thr16 = p.drop_threshold;
+    const uint32_t kpair = static_cast<uint32_t>(krow >> 1);
+    const uint32_t kshift = (krow & 1) ? 0u : 16u;
+    uint8_t* rowP = sP + wg * (AB_BLK * 128) + r * 128;
+    uint8_t* rowS = sDS + wg * (AB_BLK * 128) + r * 128;
     uint32_t it_ph = 0;
-    for (int i = i_begin; i < nblk; ++i) {
-      const int q0 = i * AB_BLK;
-      // stage LSE (times log2e) and D for the 128 queries of this block
-      if (tid < AB_BLK) {
-        const int q = q0 + tid;
-        sLSE[tid] = (q < p.T) ? p.lse[static_cast<size_t>(bh) * p.T + q] * 1.4426950408889634f : 0.f;
-      } else {
-        const int q = q0 + tid - AB_BLK;
-        sD[tid - AB_BLK] = (q < p.T) ? p.D[static_cast<size_t>(bh) * p.T + q] : 0.f;
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      mbar_wait(sdp_full, it_ph);
-      tc_fence_after();
-      const bool edge = (k0 + AB_BLK > p.T) || (q0 + AB_BLK > p.T) || (p.causal && i == jb);
-#pragma unroll 1
+
+    // One (key block, query block) tile for this thread's key row and its 64 query columns.
+    // EDGE (compile-time) adds the sequence-tail / causal predicates; interior tiles carry none.
+    auto tile_body = [&](auto edge_c, int q0) {
+      constexpr bool EDGE = decltype(edge_c)::value;
+      const bool row_ok = krow < p.T;
+      const int q_lo = p.causal ? krow : 0;   // valid queries: q_lo <= q < T
+      uint32_t vs[2][32], vd[2][32];
+      tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + wg * 64, vs[0]);
+      tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + wg * 64, vd[0]);
+#pragma unroll
       for (int c = 0; c < 2; ++c) {
         const int col0 = wg * 64 + c * 32;
-        uint32_t vs[32], vd[32];
-        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + col0, vs);
-        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + col0, vd);
         tmem_ld_wait();
+        if (c == 0) {
+          tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + wg * 64 + 32, vs[1]);
+          tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + wg * 64 + 32, vd[1]);
+        }
         float pt[32], ds[32];
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const int qi = col0 + e;
-          float pv = exp2f(__uint_as_float(vs[e]) * p.scale_log2 - sLSE[qi]);
-          float dp = __uint_as_float(vd[e]);
-          if (edge) {
-            const int q = q0 + qi;
-            if (krow >= p.T || q >= p.T || (p.causal && krow > q)) pv = 0.f;
+        for (int e4 = 0; e4 < 32; e4 += 4) {
+          const float4 l4 = *reinterpret_cast<const float4*>(sLSE + col0 + e4);
+          const float4 d4 = *reinterpret_cast<const float4*>(sD + col0 + e4);
+          const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, dd[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int e = e4 + t;
+            float pv = exp2f(fmaf(__uint_as_float(vs[c][e]), p.scale_log2, -ls[t]));
+            if (EDGE) {
+              const int q = q0 + col0 + e;
+              pv = (row_ok && q < p.T && q >= q_lo) ? pv : 0.f;
+            }
+            pt[e] = pv;
+            ds[e] = pv * (__uint_as_float(vd[c][e]) - dd[t]);
           }
-          float pd = pv;
-          if (p.drop_threshold) {
-            const uint64_t idx =
-                (static_cast<uint64_t>(bh) * p.T + (q0 + qi)) * static_cast<uint64_t>(p.T) + krow;
-            const bool keep = dropout_keep(seed, idx, p.drop_threshold);
-            pd = keep ? pv * p.drop_scale : 0.f;
-            dp = keep ? dp * p.drop_scale : 0.f;
-          }
-          pt[e] = pd;
-          ds[e] = pv * (dp - sD[qi]) * p.scale;
         }
-        uint8_t* rowP = sP + wg * (AB_BLK * 128) + r * 128;
-        uint8_t* rowS = sDS + wg * (AB_BLK * 128) + r * 128;
+        if (drop) {
+#pragma unroll
+          for (int e4 = 0; e4 < 32; e4 += 4) {
+            const uint4 k4 = *reinterpret_cast<const uint4*>(sKey + col0 + e4);
+            const uint32_t kk[4] = {k4.x, k4.y, k4.z, k4.w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const int e = e4 + t;
+              const uint32_t bits = (drop_mix(kk[t] + kpair) >> kshift) & 0xFFFFu;
+              const bool keep = bits >= thr16;
+              // dS = P * (keep ? dP/(1-p) : 0 - D);  P_drop feeds dV
+              const float pv = pt[e];
+              const float dpd = keep ? __uint_as_float(vd[c][e]) * p.drop_scale : 0.f;
+              const float dcol = *(sD + col0 + e);
+              ds[e] = pv * (dpd - dcol);
+              pt[e] = keep ? pv * p.drop_scale : 0.f;
+            }
+          }
+        }
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const int chunk = (c * 4 + g) ^ (r & 7);
@@ -248,6 +273,24 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
           *reinterpret_cast<uint4*>(rowS + chunk * 16) = u;
         }
       }
+    };
+
+    for (int i = i_begin; i < nblk; ++i) {
+      const int q0 = i * AB_BLK;
+      // stage LSE (times log2e), D and the dropout row keys for the 128 queries of this block
+      if (tid < AB_BLK) {
+        const int q = q0 + tid;
+        sLSE[tid] = (q < p.T) ? p.lse[static_cast<size_t>(bh) * p.T + q] * 1.4426950408889634f : 0.f;
+      } else {
+        const int q = q0 + tid - AB_BLK;
+        sD[tid - AB_BLK] = (q < p.T) ? p.D[static_cast<size_t>(bh) * p.T + q] : 0.f;
+        if (drop) sKey[tid - AB_BLK] = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + q);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(sdp_full, it_ph);
+      tc_fence_after();
+      const bool edge = (k0 + AB_BLK > p.T) || (q0 + AB_BLK > p.T) || (p.causal && i == jb);
+      if (edge) tile_body(std::true_type{}, q0); else tile_body(std::false_type{}, q0);
       tc_fence_before();
       fence_proxy_async();
       mbar_arrive(pds_full);
@@ -263,8 +306,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
           float* dst = p.dq_acc + static_cast<size_t>(row_base + q) * p.d + h * AB_HD + wg * 32;
 #pragma unroll
           for (int e = 0; e < 32; e += 4)
-            red_add_v4(dst + e, __uint_as_float(v[e]), __uint_as_float(v[e + 1]),
-                       __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+            red_add_v4(dst + e, __uint_as_float(v[e]) * p.scale, __uint_as_float(v[e + 1]) * p.scale,
+                       __uint_as_float(v[e + 2]) * p.scale, __uint_as_float(v[e + 3]) * p.scale);
         }
       }
       tc_fence_before();
@@ -275,6 +318,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     // The last dq_full wait above also covers the final dV / dK MMAs (same commit).
     if (i_begin < nblk) {
       const uint32_t tcol = (wg == 0) ? TC_DV : TC_DK;
+      const float oscale = (wg == 0) ? 1.f : p.scale;   // softmax scale folded out of dS
       const bool ok = krow < p.T;   // tcgen05.ld is warp-collective: only the stores are predicated
       __nv_bfloat16* dst = p.dqkv + static_cast<size_t>(row_base + (ok ? krow : k0)) * 3 * p.d +
                            (wg == 0 ? 2 * p.d : p.d) + h * AB_HD;
@@ -287,10 +331,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             uint4 u;
-            u.x = pack_bf16x2(__uint_as_float(v[g * 8 + 0]), __uint_as_float(v[g * 8 + 1]));
-            u.y = pack_bf16x2(__uint_as_float(v[g * 8 + 2]), __uint_as_float(v[g * 8 + 3]));
-            u.z = pack_bf16x2(__uint_as_float(v[g * 8 + 4]), __uint_as_float(v[g * 8 + 5]));
-            u.w = pack_bf16x2(__uint_as_float(v[g * 8 + 6]), __uint_as_float(v[g * 8 + 7]));
+            u.x = pack_bf16x2(__uint_as_float(v[g * 8 + 0]) * oscale, __uint_as_float(v[g * 8 + 1]) * oscale);
+            u.y = pack_bf16x2(__uint_as_float(v[g * 8 + 2]) * oscale, __uint_as_float(v[g * 8 + 3]) * oscale);
+            u.z = pack_bf16x2(__uint_as_float(v[g * 8 + 4]) * oscale, __uint_as_float(v[g * 8 + 5]) * oscale);
+            u.w = pack_bf16x2(__uint_as_float(v[g * 8 + 6]) * oscale, __uint_as_float(v[g * 8 + 7]) * oscale);
             *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) = u;
           }
         }
@@ -393,8 +437,8 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   p.scale_log2 = p.scale * 1.4426950408889634f;
   p.causal = causal;
   if (drop_p > 0.f && drop_p < 1.f) {
-    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
-    p.drop_scale = 1.f / (1.f - drop_p);
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 65536.0 + 0.5);  // 16-bit
+    p.drop_scale = 1.f / (1.f - p.drop_threshold / 65536.f);
   } else {
     p.drop_threshold = 0;
     p.drop_scale = 1.f;

@@ -11,11 +11,12 @@
 // Input  qkv [B*T, 3*d]  bf16, row m = b*T + t, columns [q | k | v], head h at h*64 inside each.
 // Output out [B*T, d]    bf16, head h at columns h*64 .. h*64+63;   lse [B*H, T] fp32 (natural log).
 //
-// CTA = one (batch, head, 128-row query block), 320 threads:
+// CTA = one (batch, head, 128-row query block), 384 threads (3 warpgroups, registers re-balanced
+// with setmaxnreg: 40 for the control warpgroup, 232 for the softmax warpgroups):
 //   warp 0      TMA producer: Q once, then K/V tiles of 128 keys through 3-stage rings
 //   warp 1      MMA issuer:   S[w] = Q K_j^T  (M128 N128 K64),  O_blk[w] = P[w] V_j  (M128 N64 K128)
-//   warps 2-5   softmax warpgroup 0 : even key blocks      (thread = one query row)
-//   warps 6-9   softmax warpgroup 1 : odd key blocks
+//   warps 4-7   softmax warpgroup 0 : even key blocks      (thread = one query row)
+//   warps 8-11  softmax warpgroup 1 : odd key blocks
 // Each warpgroup owns one S buffer (128 TMEM columns), one O_blk buffer (64 columns) and one P
 // buffer in shared memory (bf16, 128B-swizzled K-major so it is directly the A operand of P V), and
 // keeps its own running (max, sum, O) in registers; the two partial results are merged at the end.
@@ -23,6 +24,8 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include <type_traits>
 
 #include "b200_internal.h"
 #include "sm100_ptx.cuh"
@@ -33,7 +36,7 @@ constexpr int AT_BM = 128;       // query rows per CTA
 constexpr int AT_BN = 128;       // keys per block
 constexpr int AT_HD = 64;        // head dim
 constexpr int AT_KV_STAGES = 3;
-constexpr int AT_THREADS = 320;
+constexpr int AT_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps), warpgroups 1-2: softmax
 constexpr int AT_TILE = AT_BN * AT_HD * 2;   // 16 KiB: one [128 x 64] bf16 tile
 constexpr int AT_PBYTES = AT_BM * AT_BN * 2; // 32 KiB: one P buffer
 constexpr int AT_SMEM = AT_TILE * (1 + 2 * AT_KV_STAGES) + 2 * AT_PBYTES + 1024 /*bars+merge*/ +
@@ -51,10 +54,6 @@ struct AttnFwdParams {
   uint32_t drop_seed;
   const uint32_t* seed_ptr;
 };
-
-__device__ __forceinline__ uint64_t attn_drop_index(int bh, int q, int k, int T) {
-  return (static_cast<uint64_t>(bh) * T + q) * static_cast<uint64_t>(T) + k;
-}
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
@@ -110,6 +109,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
   const uint32_t tmem_base = *tmem_slot;
   // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384)
 
+  if (warp < 4) {
+    setmaxnreg_dec<40>();
   if (warp == 0) {
     // ================================ TMA producer ================================
     if (lane == 0) {
@@ -182,9 +183,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
         if (++vs == AT_KV_STAGES) { vs = 0; vph ^= 1; }
       }
     }
+  }
   } else {
+    setmaxnreg_inc<232>();
     // ================================ softmax warpgroups ==========================
-    const int w = (warp - 2) >> 2;        // warpgroup 0 / 1
+    const int w = (warp - 4) >> 2;        // softmax warpgroup 0 / 1
     const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
     const int quarter = warp & 3;         // TMEM lane quarter
     const int r = quarter * 32 + lane;    // query row inside the block
@@ -207,67 +210,73 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       oph ^= 1;
       tc_fence_after();
       const float alpha = exp2f(m_ref - m_prev);
+      uint32_t v0[32], v1[32];
+      tmem_ld_32x32b_x32(tO, v0);
+      tmem_ld_32x32b_x32(tO + 32, v1);
+      tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < AT_HD / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tO + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      for (int i = 0; i < 32; ++i) {
+        o[i] = o[i] * alpha + __uint_as_float(v0[i]);
+        o[32 + i] = o[32 + i] * alpha + __uint_as_float(v1[i]);
       }
       m_ref = m_prev;
     };
 
-    for (int j = w; j < nkv; j += 2) {
-      mbar_wait(&s_full[w], sph);
-      sph ^= 1;
-      tc_fence_after();
-      const int k0 = j * AT_BN;
-      const bool need_mask = (k0 + AT_BN > p.T) || (p.causal && j == qb);
-      // ---- pass 1: row maximum -------------------------------------------------------
-      float mx = NEG_BIG;
+    const uint32_t rowkey = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + qrow);
+    const bool drop = p.drop_threshold != 0;
+    const uint32_t thr16 = p.drop_threshold;   // 16-bit threshold (see host wrapper)
+
+    // One key block for this thread's query row.  MASK is a compile-time flag so that the common
+    // (interior, non-causal) blocks carry no per-element predicate; limit = first masked key.
+    auto block_body = [&](auto mask_c, int k0, int limit) {
+      constexpr bool MASK = decltype(mask_c)::value;
+      // ---- pass 1: row maximum (4 independent chains, two 64-column loads) ----------------
+      float mx[4] = {NEG_BIG, NEG_BIG, NEG_BIG, NEG_BIG};
 #pragma unroll 1
-      for (int c = 0; c < AT_BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tS + c * 32, v);
+      for (int hlf = 0; hlf < 2; ++hlf) {
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32b_x32(tS + hlf * 64, v0);
+        tmem_ld_32x32b_x32(tS + hlf * 64 + 32, v1);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(v[i]);
-          if (need_mask) {
-            const int kk = k0 + c * 32 + i;
-            if (kk >= p.T || (p.causal && kk > qrow)) s = NEG_BIG;
+          float s0 = __uint_as_float(v0[i]), s1 = __uint_as_float(v1[i]);
+          if (MASK) {
+            if (k0 + hlf * 64 + i >= limit) s0 = NEG_BIG;
+            if (k0 + hlf * 64 + 32 + i >= limit) s1 = NEG_BIG;
           }
-          mx = fmaxf(mx, s);
+          mx[i & 3] = fmaxf(mx[i & 3], fmaxf(s0, s1));
         }
       }
-      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      const float mxx = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      const float m_new = fmaxf(m_run, mxx * p.scale_log2);
       // previous block of this warpgroup: its P buffer must be free before we overwrite it
       if (n_done > 0) accumulate_prev();
-      // ---- pass 2: P = exp2(s*scale - m_new), row sum, bf16 -> swizzled smem -----------
-      float rs = 0.f;
-#pragma unroll 1
+      // ---- pass 2: P = exp2(s*scale - m_new), row sum, bf16 -> swizzled smem -----------------
+      float rs[4] = {0.f, 0.f, 0.f, 0.f};
+      const float neg_m = -m_new;
+      uint32_t va[32], vb[32];
+      tmem_ld_32x32b_x32(tS, va);
+#pragma unroll
       for (int c = 0; c < AT_BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tS + c * 32, v);
+        uint32_t(&v)[32] = (c & 1) ? vb : va;
         tmem_ld_wait();
+        if (c + 1 < AT_BN / 32) tmem_ld_32x32b_x32(tS + (c + 1) * 32, (c & 1) ? va : vb);
         float pv[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(v[i]);
-          float e = exp2f(s * p.scale_log2 - m_new);
-          if (need_mask) {
-            const int kk = k0 + c * 32 + i;
-            if (kk >= p.T || (p.causal && kk > qrow)) e = 0.f;
-          }
-          rs += e;
+          float e = exp2f(fmaf(__uint_as_float(v[i]), p.scale_log2, neg_m));
+          if (MASK) e = (k0 + c * 32 + i < limit) ? e : 0.f;
+          rs[i & 3] += e;
           pv[i] = e;
         }
-        if (p.drop_threshold) {
+        if (drop) {
+          const uint32_t kp = rowkey + static_cast<uint32_t>((k0 + c * 32) >> 1);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const uint64_t idx = attn_drop_index(bh, qrow, k0 + c * 32 + i, p.T);
-            pv[i] = dropout_keep(seed, idx, p.drop_threshold) ? pv[i] * p.drop_scale : 0.f;
+          for (int t = 0; t < 16; ++t) {
+            const uint32_t wd = drop_mix(kp + t);
+            pv[2 * t] = ((wd >> 16) >= thr16) ? pv[2 * t] * p.drop_scale : 0.f;
+            pv[2 * t + 1] = ((wd & 0xFFFFu) >= thr16) ? pv[2 * t + 1] * p.drop_scale : 0.f;
           }
         }
         // 32 keys = 4 x 16-byte chunks of the 128-byte swizzled row; chunk index XOR (row & 7)
@@ -283,9 +292,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
           *reinterpret_cast<uint4*>(dst + chunk * 16) = u;
         }
       }
-      l_run = l_run * exp2f(m_run - m_new) + rs;
+      l_run = l_run * exp2f(m_run - m_new) + ((rs[0] + rs[1]) + (rs[2] + rs[3]));
       m_run = m_new;
       m_prev = m_new;
+    };
+
+    for (int j = w; j < nkv; j += 2) {
+      mbar_wait(&s_full[w], sph);
+      sph ^= 1;
+      tc_fence_after();
+      const int k0 = j * AT_BN;
+      const bool need_mask = (k0 + AT_BN > p.T) || (p.causal && j == qb);
+      if (need_mask) {
+        const int limit = p.causal ? min(p.T, qrow + 1) : p.T;
+        block_body(std::true_type{}, k0, limit);
+      } else {
+        block_body(std::false_type{}, k0, 0);
+      }
       tc_fence_before();
       fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core
       mbar_arrive(&p_full[w]);
@@ -368,8 +391,8 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B,
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(head_dim));
   p.causal = causal;
   if (drop_p > 0.f && drop_p < 1.f) {
-    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
-    p.drop_scale = 1.f / (1.f - drop_p);
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 65536.0 + 0.5);  // 16-bit
+    p.drop_scale = 1.f / (1.f - p.drop_threshold / 65536.f);
   } else {
     p.drop_threshold = 0;
     p.drop_scale = 1.f;

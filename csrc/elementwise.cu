@@ -177,17 +177,20 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 
 // ----------------------------------------------------------------------------------------
 // Column reductions over rows (bias gradients; LayerNorm gamma/beta gradients).
-// Stage 1: grid (ceil(N/256), R): block = 32 column-vectors x 8 row lanes, each thread owns
-//          8 columns; per-block partial sums -> scratch[R][K][N] (fp32).
-// Stage 2: sum the R partials, write bf16 (optionally accumulating into the destination).
+// grid (ceil(N/256), R): block = 32 column-vectors x 8 row lanes, each thread owns 8 columns;
+// per-block partial sums -> scratch[R][K][N] (fp32); the last CTA of each column block to finish
+// (completion counter at the head of the scratch buffer, self-resetting) sums the R partials and writes bf16,
+// optionally accumulating into the destination.  The counter region must be zero before the
+// FIRST call on a scratch buffer.
 //   MODE 0: out0[n] = sum_m dy[m,n]
 //   MODE 1: out0[n] = sum_m dy[m,n] * xhat[m,n]  (dgamma),  out1[n] = sum_m dy[m,n]  (dbeta)
 // ----------------------------------------------------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(256)
-colreduce_stage1_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                        const float* __restrict__ mean, const float* __restrict__ rstd,
-                        float* __restrict__ scratch, int M, int N, int ld) {
+colreduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                 const float* __restrict__ mean, const float* __restrict__ rstd,
+                 float* __restrict__ scratch, unsigned int* __restrict__ counters, int M, int N, int ld,
+                 __nv_bfloat16* __restrict__ out0, __nv_bfloat16* __restrict__ out1, int accumulate) {
   constexpr int K = (MODE == 1) ? 2 : 1;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int col = (blockIdx.x * 32 + tx) * 8;
@@ -216,12 +219,13 @@ colreduce_stage1_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
     }
   }
   __shared__ float red[8][K][32][9];  // +1 padding against bank conflicts
+  __shared__ bool is_last;
 #pragma unroll
   for (int k = 0; k < K; ++k)
 #pragma unroll
     for (int j = 0; j < 8; ++j) red[ty][k][tx][j] = acc[k][j];
   __syncthreads();
-  // 256 threads: thread t finalises (k, column-in-block) pairs
+  const int R = gridDim.y;
   for (int idx = threadIdx.x; idx < K * 256; idx += 256) {
     const int k = idx / 256, c = idx % 256;
     const int gcol = blockIdx.x * 256 + c;
@@ -232,19 +236,29 @@ colreduce_stage1_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
       scratch[(static_cast<size_t>(blockIdx.y) * K + k) * N + gcol] = s;
     }
   }
-}
-
-__global__ void colreduce_stage2_kernel(const float* __restrict__ scratch, int R, int K, int N,
-                                        __nv_bfloat16* __restrict__ out0,
-                                        __nv_bfloat16* __restrict__ out1, int accumulate) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= K * N) return;
-  const int k = idx / N, n = idx % N;
-  float s = 0.f;
-  for (int r = 0; r < R; ++r) s += scratch[(static_cast<size_t>(r) * K + k) * N + n];
-  __nv_bfloat16* out = (k == 0) ? out0 : out1;
-  if (accumulate) s += __bfloat162float(out[n]);
-  out[n] = __float2bfloat16(s);
+  // The last CTA of each column block to finish folds the R partials (threadfence-reduction).
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(&counters[blockIdx.x], 1u);
+    is_last = (prev == static_cast<unsigned int>(R - 1));
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int idx = threadIdx.x; idx < K * 256; idx += 256) {
+    const int k = idx / 256, c = idx % 256;
+    const int gcol = blockIdx.x * 256 + c;
+    if (gcol < N) {
+      float s = 0.f;
+#pragma unroll 8
+      for (int r = 0; r < R; ++r) s += __ldcg(&scratch[(static_cast<size_t>(r) * K + k) * N + gcol]);
+      __nv_bfloat16* out = (k == 0) ? out0 : out1;
+      if (accumulate) s += __bfloat162float(out[gcol]);
+      out[gcol] = __float2bfloat16(s);
+    }
+  }
+  if (threadIdx.x == 0) counters[blockIdx.x] = 0;  // leave the counters ready for the next call
 }
 
 // ----------------------------------------------------------------------------------------
@@ -591,14 +605,19 @@ static inline int grid_for(size_t work_items, int threads, int per_sm) {
   return static_cast<int>(blocks);
 }
 
-// rows-per-split for the column reductions
+constexpr int kColreduceCounters = 256;
+// number of row splits for the column reductions: about one CTA per SM in total
 static inline int colreduce_splits(int M, int N) {
   const int gx = (N + 255) / 256;
-  int R = (2 * device_sm_count() + gx - 1) / gx;
-  const int max_r = (M + 7) / 8;
+  int R = (device_sm_count() + gx - 1) / gx;
+  const int max_r = (M + 31) / 32;
   if (R > max_r) R = max_r;
+  if (R > 64) R = 64;
   if (R < 1) R = 1;
   return R;
+}
+static inline size_t colreduce_partial_floats(int M, int N, int outputs) {
+  return (static_cast<size_t>(colreduce_splits(M, N)) * outputs * N + 63) / 64 * 64;
 }
 
 }  // namespace b200
@@ -639,7 +658,10 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
 }
 
 extern "C" size_t b200_colreduce_scratch_bytes(int M, int N, int outputs) {
-  return static_cast<size_t>(colreduce_splits(M, N)) * outputs * N * sizeof(float);
+  // 256 completion counters (one per 256-column block, fixed place at the head of the buffer so that
+  // calls with different shapes can share one scratch buffer) + fp32 partials [splits][outputs][N]
+  return kColreduceCounters * sizeof(unsigned int) +
+         colreduce_partial_floats(M, N, outputs) * sizeof(float);
 }
 
 extern "C" int b200_layernorm_bwd_params(const void* dy, const void* x, const float* mean,
@@ -651,12 +673,13 @@ extern "C" int b200_layernorm_bwd_params(const void* dy, const void* x, const fl
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int R = colreduce_splits(M, d);
   dim3 grid((d + 255) / 256, R);
-  colreduce_stage1_kernel<1><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy),
-                                                  static_cast<const __nv_bfloat16*>(x), mean, rstd,
-                                                  static_cast<float*>(scratch), M, d, d);
-  colreduce_stage2_kernel<<<(2 * d + 255) / 256, 256, 0, s>>>(
-      static_cast<const float*>(scratch), R, 2, d, static_cast<__nv_bfloat16*>(dgamma),
-      static_cast<__nv_bfloat16*>(dbeta), accumulate);
+  if ((d + 255) / 256 > kColreduceCounters) return -3;
+  unsigned int* counters = static_cast<unsigned int*>(scratch);
+  float* part = reinterpret_cast<float*>(counters + kColreduceCounters);
+  colreduce_kernel<1><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy),
+                                           static_cast<const __nv_bfloat16*>(x), mean, rstd, part,
+                                           counters, M, d, d, static_cast<__nv_bfloat16*>(dgamma),
+                                           static_cast<__nv_bfloat16*>(dbeta), accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -667,12 +690,12 @@ extern "C" int b200_colsum(const void* dy, void* out, int M, int N, int ld, int 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int R = colreduce_splits(M, N);
   dim3 grid((N + 255) / 256, R);
-  colreduce_stage1_kernel<0><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), nullptr,
-                                                  nullptr, nullptr, static_cast<float*>(scratch), M,
-                                                  N, ld);
-  colreduce_stage2_kernel<<<(N + 255) / 256, 256, 0, s>>>(static_cast<const float*>(scratch), R, 1,
-                                                          N, static_cast<__nv_bfloat16*>(out),
-                                                          nullptr, accumulate);
+  if ((N + 255) / 256 > kColreduceCounters) return -3;
+  unsigned int* counters = static_cast<unsigned int*>(scratch);
+  float* part = reinterpret_cast<float*>(counters + kColreduceCounters);
+  colreduce_kernel<0><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), nullptr, nullptr,
+                                           nullptr, part, counters, M, N, ld,
+                                           static_cast<__nv_bfloat16*>(out), nullptr, accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 

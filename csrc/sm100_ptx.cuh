@@ -225,6 +225,16 @@ __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// Register re-distribution between warpgroups (must be executed by all 4 warps of a warpgroup).
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
+
 // ----------------------------------------------------------------------------------------
 // UMMA descriptors
 // ----------------------------------------------------------------------------------------
@@ -281,6 +291,19 @@ __device__ __forceinline__ bool dropout_keep(uint32_t seed, uint64_t idx, uint32
   uint32_t h = hash_u32(static_cast<uint32_t>(idx) ^ seed);
   h = hash_u32(h + static_cast<uint32_t>(idx >> 32) * 0x9E3779B9U + 0x85ebca6bU);
   return h >= threshold;  // threshold = p * 2^32
+}
+// Row-keyed dropout for attention probabilities: one 32-bit mix per PAIR of keys, 16 random bits
+// per element.  key k of query row q uses  word = drop_mix(drop_rowkey(seed, row(q)) + (k >> 1)),
+// bits = (k & 1) ? word & 0xFFFF : word >> 16,  keep = bits >= thr16  (thr16 = p * 65536).
+__device__ __forceinline__ uint32_t drop_rowkey(uint32_t seed, uint32_t row_index) {
+  return hash_u32(seed ^ hash_u32(row_index + 0x9E3779B9U));
+}
+__device__ __forceinline__ uint32_t drop_mix(uint32_t x) {
+  x *= 0x9E3779B1U;
+  x ^= x >> 15;
+  x *= 0x85EBCA77U;
+  x ^= x >> 16;
+  return x;
 }
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));

@@ -54,7 +54,9 @@ int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void*
 /* dx = LayerNorm'(dy) + dres (dres may be NULL) */
 int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                        const float* rstd, const void* dres, void* dx, int M, int d, void* stream);
-/* Scratch (fp32 partial sums) needed by the two column reductions below. */
+/* Scratch needed by the two column reductions below: 256 per-column-block completion
+ * counters followed by fp32 partial sums.  The buffer must be zero-filled once before its first use; every call
+ * leaves the counters zeroed again.  Calls sharing one scratch buffer must be stream-ordered. */
 size_t b200_colreduce_scratch_bytes(int M, int N, int outputs);
 /* dgamma[n] (+)= sum_m dy*xhat, dbeta[n] (+)= sum_m dy.  scratch >= colreduce_scratch_bytes(M,d,2) */
 int b200_layernorm_bwd_params(const void* dy, const void* x, const float* mean, const float* rstd,
