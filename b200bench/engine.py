@@ -66,8 +66,19 @@ class NativeEngine:
         dev = device
 
         # ---- parameters / gradients / optimizer state ---------------------------------------
-        self.params = torch.zeros(Lt.total, dtype=BF16, device=dev)
-        self.grads = torch.zeros(Lt.total, dtype=BF16, device=dev)
+        self.comm_mode = comm if ws > 1 else "none"
+        self.comm = None
+        if ws > 1 and comm == "fused":
+            from .parallel.peer import PeerComm
+
+            self.comm = PeerComm(ctx, device)
+            # symmetric buffers: every rank can address every peer's weights and gradients
+            self.params_pb = self.comm.alloc("params", Lt.total, BF16)
+            self.grads_pb = self.comm.alloc("grads", Lt.total, BF16)
+            self.params, self.grads = self.params_pb.tensor, self.grads_pb.tensor
+        else:
+            self.params = torch.zeros(Lt.total, dtype=BF16, device=dev)
+            self.grads = torch.zeros(Lt.total, dtype=BF16, device=dev)
         self._init_params(seed)
         if ws > 1:
             ctx.broadcast(self.params, 0)
@@ -126,15 +137,14 @@ class NativeEngine:
         self.ops.step_seed_register(self.step_seed)
 
         self.use_graph = use_graph
-        self._graphs: Dict[bool, torch.cuda.CUDAGraph] = {}
+        self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self._warm = 0
-        self.comm_mode = comm
-        self.comm = None
-        if ws > 1 and comm == "fused":
-            from .parallel.peer import PeerComm
-
-            self.comm = PeerComm(ctx, device, self)
         self._launches_per_step: Optional[int] = None
+        # DDP gradient buckets = one per transformer block + (embeddings, final LN)   [SURVEY N3]
+        l0 = Lt.layer_range(0)[0]
+        l1 = Lt.layer_range(self.L - 1)[1]
+        self._bucket_head = (0, l0)
+        self._bucket_tail = (l1, Lt.total)
 
     # ---------------------------------------------------------------------------------------
     def _init_params(self, seed: int) -> None:
@@ -182,8 +192,9 @@ class NativeEngine:
                         self.statf[0], self.statf[1])
         o.linear_fwd(self.lnf, P["transformer.wte.weight"], self.logits)
 
-    def _loss_and_backward(self, first_micro: bool) -> None:
+    def _loss_and_backward(self, first_micro: bool, last_micro: bool) -> None:
         o, P, G, p = self.ops, self.P, self.G, self.dropout
+        reduce_now = self.comm is not None and self.strategy == "ddp" and last_micro
         B, T, d, H, hd, M, V = self.B, self.T, self.d, self.H, self.hd, self.M, self.V
         acc = not first_micro
         o.cross_entropy(self.logits, self.targets, self.loss_rows, self.n_valid, self.loss, M, V,
@@ -225,34 +236,44 @@ class NativeEngine:
             o.layernorm_bwd(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres, dres=self.dmid)
             o.layernorm_bwd_params(self.dln, self.x[l], st[0], st[1], G[pre + "ln_1.weight"],
                                    G[pre + "ln_1.bias"], self.scratch, acc)
-            if self.comm is not None:
-                self.comm.layer_backward_done(l)
+            if reduce_now:
+                # K13: this block's gradients are final -> all-reduce them on the comm stream while
+                # the compute stream continues with block l-1 (overlap with backward)
+                a, b = self.layout.layer_range(l)
+                self.comm.fork()
+                self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
         o.embedding_bwd(self.tokens, self.dres, G["transformer.wte.weight"], G["transformer.wpe.weight"],
                         B, T, d, p, self._seed(-1, 0), accumulate_wpe=acc)
+        if reduce_now:
+            self.comm.fork()
+            for a, b in (self._bucket_tail, self._bucket_head):
+                self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
+            self.comm.join()
 
     # ---------------------------------------------------------------------------------------
-    def _micro_step(self, first_micro: bool) -> None:
+    def _micro_step(self, first_micro: bool, last_micro: bool) -> None:
         if self.dropout > 0:
             self.ops.step_seed_advance()      # new dropout masks every micro-step, also under graph replay
         self._forward()
-        self._loss_and_backward(first_micro)
+        self._loss_and_backward(first_micro, last_micro)
 
-    def _run_micro(self, first_micro: bool) -> None:
+    def _run_micro(self, first_micro: bool, last_micro: bool) -> None:
         if not self.use_graph:
-            self._micro_step(first_micro)
+            self._micro_step(first_micro, last_micro)
             return
-        g = self._graphs.get(first_micro)
+        key = (first_micro, last_micro)
+        g = self._graphs.get(key)
         if g is None:
             if self._warm < 2:              # eager warm-up: function attributes, tensor maps, lazy init
                 self._warm += 1
-                self._micro_step(first_micro)
+                self._micro_step(first_micro, last_micro)
                 return
             before = self.ops.launches
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._micro_step(first_micro)
+                self._micro_step(first_micro, last_micro)
             self._graph_launches = self.ops.launches - before
-            self._graphs[first_micro] = g
+            self._graphs[key] = g
         g.replay()
 
     def _set_hp(self, grad_scale: float) -> None:
@@ -270,8 +291,22 @@ class NativeEngine:
         scale = 1.0 / ws
         clip = self.cfg.optim.grad_clip > 0
         if self.comm is not None:
+            if self.strategy == "ddp":          # gradients were all-reduced and scaled during backward (K13)
+                self._set_hp(1.0)
+                gn = None
+                if clip:
+                    self.gnorm_sq.zero_()
+                    self.ops.sumsq(self.grads, self.gnorm_sq, 1.0)
+                    gn = self.gnorm_sq
+                self.ops.adamw_flat(self.master, self.exp_avg, self.exp_avg_sq, self.grads, self.params, self.hp, gn)
+                return
+            # K15: pull + reduce my partition, clip, AdamW, store updated weights (to all ranks for ZeRO-2)
             self._set_hp(scale)
-            self.comm.boundary(clip)
+            self.comm.rs_adamw(self.grads_pb, self.params_pb, self.lo, self.hi - self.lo, self.master,
+                               self.exp_avg, self.exp_avg_sq, self.grad_shard, self.hp,
+                               push_all=(self.strategy == "zero2"))
+            if self.strategy in SHARDED_PARAMS:
+                ctx.all_gather(self.params[self.lo:self.hi], self.params)   # until K14 gathers per GEMM
             return
         if self.strategy == "ddp":
             if ws > 1:
@@ -303,8 +338,9 @@ class NativeEngine:
         else:
             self.targets.copy_(targets, non_blocking=True)
         first = (self.micro % self.accum) == 0
+        last = ((self.micro + 1) % self.accum) == 0
         before = self.ops.launches
-        self._run_micro(first)
+        self._run_micro(first, last)
         self.micro += 1
         if self.micro % self.accum == 0:
             self._optimizer_boundary()

@@ -1,7 +1,164 @@
-"""Peer-memory communication runtime (placeholder until csrc/comm_*.cu lands in this round)."""
+"""Peer-memory communication runtime: symmetric buffers mapped into every rank, flag words, and
+the Python front-end of the fused collective kernels in ``csrc/comm.cu``.
+
+The reference's whole communication layer is ``init_process_group('nccl', tcp://...)`` plus what
+DDP / FSDP / DeepSpeed do internally (``benchmarking/train_harness.py:186-204,217-271``; SURVEY.md
+§2.7 N1-N10, §5.8).  Here ``torch.distributed`` is kept for rendezvous only (N1): it carries the
+64-byte CUDA IPC handles of each rank's buffers.  After that every rank holds device pointers to
+every peer's gradient buffer, weight buffer and flag words, and the collectives are single kernels
+that read and write those pointers over NVLink (K13 all-reduce+scale, K15 reduce-scatter+AdamW+push).
+
+Buffers are allocated with ``cudaMalloc`` inside the native library (IPC cannot export PyTorch's
+caching-allocator blocks) and wrapped as torch tensors without a copy.
+"""
 from __future__ import annotations
+
+import ctypes
+from ctypes import c_float, c_int, c_size_t, c_void_p
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import ops as _ops
+from .collectives import DistCtx
+
+
+class _RawCuda:
+    """Minimal ``__cuda_array_interface__`` holder so torch can view raw device memory."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+class PeerBuffer:
+    def __init__(self, name: str, local_ptr: int, nbytes: int, peer_ptrs: List[int], tensor: torch.Tensor):
+        self.name, self.local_ptr, self.nbytes, self.peer_ptrs, self.tensor = name, local_ptr, nbytes, peer_ptrs, tensor
+        self.table = (c_void_p * len(peer_ptrs))(*peer_ptrs)      # host array of device pointers
 
 
 class PeerComm:
-    def __init__(self, ctx, device, engine):
-        raise NotImplementedError("fused peer-memory collectives are not built yet: use --comm nccl")
+    def __init__(self, ctx: DistCtx, device: torch.device, comm_ctas: int = 64):
+        if not ctx.active:
+            raise RuntimeError("PeerComm needs an initialised process group (world_size > 1)")
+        self.ctx, self.device = ctx, device
+        self.rank, self.ws = ctx.rank, ctx.world_size
+        if self.ws not in (2, 4, 8):
+            raise NotImplementedError("fused collectives are instantiated for world sizes 2, 4 and 8")
+        self.ops = _ops.load()
+        L = self.ops.lib
+        vp, i, f, sz = c_void_p, c_int, c_float, c_size_t
+        L.b200_peer_alloc.argtypes = [sz, ctypes.POINTER(vp), vp]
+        L.b200_peer_open.argtypes = [vp, ctypes.POINTER(vp)]
+        L.b200_peer_close.argtypes = [vp]
+        L.b200_peer_free.argtypes = [vp]
+        L.b200_comm_flag_bytes.restype = sz
+        L.b200_comm_allreduce.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
+        L.b200_comm_rs_adamw.argtypes = [vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, i, vp]
+        L.b200_comm_push_ranges.argtypes = [vp, vp, i, i, vp, i, vp]
+        L.b200_peer_copy.argtypes = [vp, vp, sz, i, vp]
+        self.buffers: Dict[str, PeerBuffer] = {}
+        self.comm_ctas = comm_ctas
+        self.flags = self.alloc("flags", int(L.b200_comm_flag_bytes()), torch.uint8)
+        self.stream = torch.cuda.Stream(device=device)
+        self._ev_ready = torch.cuda.Event()
+        self._ev_done = torch.cuda.Event()
+        self._forked = False
+        self.bytes_allocated = 0
+
+    # ---- symmetric allocation -------------------------------------------------------------------
+    def alloc(self, name: str, numel: int, dtype: torch.dtype) -> PeerBuffer:
+        """Every rank must call this with the same arguments, in the same order."""
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        nbytes = (nbytes + 255) // 256 * 256
+        ptr = c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        rc = self.ops.lib.b200_peer_alloc(nbytes, ctypes.byref(ptr), ctypes.cast(handle, c_void_p))
+        if rc:
+            raise _ops.NativeError(f"peer_alloc({name}, {nbytes}) failed with CUDA error {rc}")
+        handles: List[Optional[bytes]] = [None] * self.ws
+        dist.all_gather_object(handles, bytes(handle))
+        peer_ptrs: List[int] = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                peer_ptrs.append(ptr.value)
+                continue
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+            pp = c_void_p()
+            rc = self.ops.lib.b200_peer_open(ctypes.cast(buf, c_void_p), ctypes.byref(pp))
+            if rc:
+                raise _ops.NativeError(f"peer_open({name}, rank {r}) failed with CUDA error {rc}")
+            peer_ptrs.append(pp.value)
+        t = torch.as_tensor(_RawCuda(ptr.value, nbytes), device=self.device).view(dtype)[:numel]
+        pb = PeerBuffer(name, ptr.value, nbytes, peer_ptrs, t)
+        self.buffers[name] = pb
+        self.bytes_allocated = getattr(self, "bytes_allocated", 0) + nbytes
+        dist.barrier()
+        return pb
+
+    # ---- stream plumbing: comm kernels run on a side stream, forked from / joined to compute ------
+    def fork(self) -> None:
+        """Make the comm stream wait for everything issued so far on the current stream."""
+        self._ev_ready.record(torch.cuda.current_stream())
+        self.stream.wait_event(self._ev_ready)
+        self._forked = True
+
+    def join(self) -> None:
+        if self._forked:
+            self._ev_done.record(self.stream)
+            torch.cuda.current_stream().wait_event(self._ev_done)
+            self._forked = False
+
+    # ---- collectives -------------------------------------------------------------------------------
+    def allreduce(self, buf: PeerBuffer, off: int, n: int, scale: float, side_stream: bool = True) -> None:
+        s = self.stream if side_stream else torch.cuda.current_stream()
+        rc = self.ops.lib.b200_comm_allreduce(buf.table, self.flags.table, self.rank, self.ws, off, n, scale,
+                                              self.comm_ctas, c_void_p(s.cuda_stream))
+        if rc:
+            raise _ops.NativeError(f"comm_allreduce failed with code {rc}")
+        self.ops.launches += 2
+
+    def rs_adamw(self, grads: PeerBuffer, weights: PeerBuffer, lo: int, n: int, master, m, v, gshard, hp,
+                 push_all: bool, gnorm_out=None, ctas: int = 128) -> None:
+        s = torch.cuda.current_stream()
+        p = lambda t: c_void_p(t.data_ptr()) if t is not None else c_void_p(0)  # noqa: E731
+        rc = self.ops.lib.b200_comm_rs_adamw(grads.table, weights.table, self.flags.table, self.rank, self.ws,
+                                             lo, n, p(master), p(m), p(v), p(gshard), p(hp), int(push_all),
+                                             p(gnorm_out), ctas, c_void_p(s.cuda_stream))
+        if rc:
+            raise _ops.NativeError(f"comm_rs_adamw failed with code {rc}")
+        self.ops.launches += 2
+
+    def push_ranges(self, weights: PeerBuffer, ranges_dev: torch.Tensor) -> None:
+        s = torch.cuda.current_stream()
+        rc = self.ops.lib.b200_comm_push_ranges(weights.table, self.flags.table, self.rank, self.ws,
+                                                c_void_p(ranges_dev.data_ptr()), ranges_dev.shape[0],
+                                                c_void_p(s.cuda_stream))
+        if rc:
+            raise _ops.NativeError(f"comm_push_ranges failed with code {rc}")
+        self.ops.launches += 2
+
+    def peer_copy(self, src_ptr: int, dst: torch.Tensor, nbytes: int, ctas: int = 64) -> None:
+        rc = self.ops.lib.b200_peer_copy(c_void_p(src_ptr), c_void_p(dst.data_ptr()), nbytes, ctas,
+                                         c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc:
+            raise _ops.NativeError(f"peer_copy failed with code {rc}")
+        self.ops.launches += 1
+
+    def extra_memory_bytes(self) -> int:
+        return int(self.bytes_allocated)
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)
+        if dist.is_initialized():
+            dist.barrier()
+        for pb in self.buffers.values():
+            for r, pp in enumerate(pb.peer_ptrs):
+                if r != self.rank:
+                    self.ops.lib.b200_peer_close(c_void_p(pp))
+        if dist.is_initialized():
+            dist.barrier()
+        for pb in self.buffers.values():
+            pb.tensor = None
+            self.ops.lib.b200_peer_free(c_void_p(pb.local_ptr))
+        self.buffers.clear()

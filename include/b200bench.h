@@ -94,6 +94,31 @@ int b200_sumsq(const void* grad, size_t n, float scale, float* out, void* stream
 int b200_dropout_apply(const void* in, void* out, int M, int N, float drop_p, unsigned int seed,
                        void* stream);
 
+/* ---- peer memory + fused collectives over NVLink / NVSwitch -----------
+ * b200_peer_alloc cudaMallocs a zero-filled buffer and returns its 64-byte CUDA IPC handle;
+ * b200_peer_open maps a peer's handle.  These two are the only entry points that allocate. */
+int b200_peer_alloc(size_t bytes, void** ptr, void* handle64);
+int b200_peer_open(const void* handle64, void** ptr);
+int b200_peer_close(void* ptr);
+int b200_peer_free(void* ptr);
+size_t b200_comm_flag_bytes(void);
+/* In the calls below `grads` / `weights` / `flags` are host arrays of ws device pointers: entry r is
+ * rank r's buffer as mapped in THIS process.  All ranks must issue the same sequence of calls.
+ * K13: grads[off, off+n) = scale * sum over ranks, in place on every rank (DDP, TH:217-222,374). */
+int b200_comm_allreduce(void* const* grads, void* const* flags, int rank, int ws, size_t off,
+                        size_t n, float scale, int ctas, void* stream);
+/* K15: this rank's partition [lo, lo+n): g = sum over ranks of grads; optional global-norm clip
+ * (hp[8]); AdamW on fp32 master/m/v; bf16 weights stored to every rank (push_all=1, ZeRO-2) or to
+ * the own buffer only (ZeRO-3 / FSDP).  gshard: n bf16 of local scratch. hp as in b200_adamw. */
+int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* flags, int rank,
+                       int ws, size_t lo, size_t n, float* master, float* m, float* v, void* gshard,
+                       const float* hp, int push_all, float* gnorm_out, int ctas, void* stream);
+/* Copies owned small ranges (device array of (offset, length) pairs, elements) to every peer. */
+int b200_comm_push_ranges(void* const* weights, void* const* flags, int rank, int ws,
+                          const long long* ranges_dev, int n_ranges, void* stream);
+/* dst[i] = src[i] with 16-byte volatile loads: P2P bandwidth probe when src is peer memory. */
+int b200_peer_copy(const void* src, void* dst, size_t bytes, int ctas, void* stream);
+
 /* Per-step dropout seed: a device word XORed into every dropout seed.  Register once, then launch
  * b200_step_seed_advance at the start of each micro-step (capturable in a CUDA graph). */
 int b200_step_seed_register(unsigned int* device_word);
