@@ -6,20 +6,25 @@ What the reference does through ``nn.Module`` + autograd + ``torch.optim`` / Dee
 K1-K12, §3.4).  Parameters, gradients and optimizer state live in the flat layout of
 ``models/layout.py``; activations are pre-allocated once for the fixed (batch, seq_len) of the
 run, which makes the whole micro-step a static launch sequence that is captured into a CUDA
-graph and replayed (launch-bound at tier A, batch 1: ~600 kernels per step).
+graph and replayed (launch-bound at tier A, batch 1: ~500 kernels per step).
 
-Strategies differ only in what happens at the accumulation boundary:
-    ddp    all-reduce(grads) -> AdamW on the full flat buffer
-    zero2  reduce-scatter(grads) -> clip -> AdamW on the local shard -> all-gather(weights)
-    fsdp / zero3   same arithmetic as zero2 but the bf16 weights are owned shard-wise and gathered
-           before use (per step here; per block inside the consuming GEMM with the fused path)
-``comm="fused"`` uses the peer-memory kernels of ``csrc/comm_*.cu``; ``comm="nccl"`` keeps the same
-schedule on ``torch.distributed`` collectives for A/B comparison.
+Strategies and their communication (``--comm fused``, kernels in ``csrc/comm.cu`` and
+``csrc/gemm_sm100.cu``; ``--comm nccl`` keeps the same schedule on NCCL collectives for A/B runs):
+
+ddp     full replica; K13 all-reduce(+1/N scale) per transformer block on a side stream while
+        backward continues; AdamW over the whole flat buffer                       [TH:217-222]
+zero2   weights replicated, gradients + optimizer state partitioned; K15 = pull-reduce of the
+        partition + global-norm clip + AdamW + bf16 weight push to every peer, one kernel
+                                                            [configs/deepspeed/zero2.json:10-44]
+fsdp /  weights, gradients and optimizer state partitioned (matrix region of the layout); K14: each
+zero3   weight matrix is gathered from the owners' shards INSIDE the GEMM that consumes it (forward
+        and again in dgrad), K15 updates the local shard; the vector tail (biases, LayerNorm) stays
+        replicated like DeepSpeed's persistence threshold        [TH:231-237, zero3.json:10-27]
 """
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import torch
 
@@ -31,6 +36,7 @@ from .parallel.collectives import DistCtx
 from .parallel.torch_engine import SHARDED_OPT, SHARDED_PARAMS, effective_grad_accum
 
 BF16 = torch.bfloat16
+BIG_SUFFIXES = ("attn.in_proj_weight", "attn.out_proj.weight", "mlp.0.weight", "mlp.2.weight")
 
 
 def _mix(*xs: int) -> int:
@@ -65,38 +71,49 @@ class NativeEngine:
         Lt = self.layout
         dev = device
 
-        # ---- parameters / gradients / optimizer state ---------------------------------------
+        # ---- communication runtime ------------------------------------------------------------
         self.comm_mode = comm if ws > 1 else "none"
         self.comm = None
         if ws > 1 and comm == "fused":
             from .parallel.peer import PeerComm
 
             self.comm = PeerComm(ctx, device)
-            # symmetric buffers: every rank can address every peer's weights and gradients
-            self.params_pb = self.comm.alloc("params", Lt.total, BF16)
-            self.grads_pb = self.comm.alloc("grads", Lt.total, BF16)
-            self.params, self.grads = self.params_pb.tensor, self.grads_pb.tensor
+        self.sharded_params = self.comm is not None and strategy in SHARDED_PARAMS
+
+        # ---- parameters / gradients ---------------------------------------------------------------
+        if self.comm is not None:
+            self.grads_pb = self.comm.alloc("grads", Lt.total, BF16)      # every peer can read them
+            self.grads = self.grads_pb.tensor
         else:
-            self.params = torch.zeros(Lt.total, dtype=BF16, device=dev)
             self.grads = torch.zeros(Lt.total, dtype=BF16, device=dev)
-        self._init_params(seed)
+        if self.comm is not None and not self.sharded_params:
+            self.params_pb = self.comm.alloc("params", Lt.total, BF16)    # every peer can write them
+            full = self.params_pb.tensor
+        else:
+            full = torch.zeros(Lt.total, dtype=BF16, device=dev)           # temporary when sharded
+        self._init_params(full, seed)
         if ws > 1:
-            ctx.broadcast(self.params, 0)
-        self.lo, self.hi = Lt.shard_range(rank) if strategy in SHARDED_OPT else (0, Lt.total)
+            ctx.broadcast(full, 0)                                          # N2 / N9
+        self.hp = torch.zeros(16, dtype=torch.float32, device=dev)
+        self.hp_small = torch.zeros(16, dtype=torch.float32, device=dev)
+        self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.gnorm2 = torch.zeros(2, dtype=torch.float32, device=dev)      # K15: norm, norm^2
+        self.opt_step = 0
+        self.micro = 0
+        self.G: Dict[str, torch.Tensor] = {s.name: self.grads[s.offset:s.offset + s.numel].view(s.shape)
+                                           for s in Lt}
+        if self.sharded_params:
+            self._setup_sharded(full)
+            del full
+        else:
+            self.params = full
+            self.lo, self.hi = Lt.shard_range(rank) if strategy in SHARDED_OPT else (0, Lt.total)
+            self.master = self.params[self.lo:self.hi].float()
+            self.P = {s.name: self.params[s.offset:s.offset + s.numel].view(s.shape) for s in Lt}
         n_opt = self.hi - self.lo
-        self.master = self.params[self.lo:self.hi].float()
         self.exp_avg = torch.zeros(n_opt, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n_opt, dtype=torch.float32, device=dev)
         self.grad_shard = torch.zeros(n_opt, dtype=BF16, device=dev) if strategy in SHARDED_OPT else None
-        self.hp = torch.zeros(16, dtype=torch.float32, device=dev)
-        self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=dev)
-        self.opt_step = 0
-        self.micro = 0
-        self.params_stale = False
-        self.P: Dict[str, torch.Tensor] = {s.name: self.params[s.offset:s.offset + s.numel].view(s.shape)
-                                           for s in Lt}
-        self.G: Dict[str, torch.Tensor] = {s.name: self.grads[s.offset:s.offset + s.numel].view(s.shape)
-                                           for s in Lt}
 
         # ---- activations (allocated once) -----------------------------------------------------
         M, d, V, L = self.M, self.d, self.V, self.L
@@ -139,22 +156,24 @@ class NativeEngine:
         self.use_graph = use_graph
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self._warm = 0
+        self._graph_launches = 0
         self._launches_per_step: Optional[int] = None
-        # DDP gradient buckets = one per transformer block + (embeddings, final LN)   [SURVEY N3]
-        l0 = Lt.layer_range(0)[0]
-        l1 = Lt.layer_range(self.L - 1)[1]
-        self._bucket_head = (0, l0)
-        self._bucket_tail = (l1, Lt.total)
+        # DDP gradient buckets = the matrices of one transformer block each + (embeddings) + (vector tail)
+        self._bucket_head = (0, Lt.layer_range(0)[0])
+        self._bucket_tail = (Lt.layer_range(self.L - 1)[1], Lt.total)
+        if ws > 1:
+            torch.cuda.synchronize(dev)
+            ctx.barrier()
 
     # ---------------------------------------------------------------------------------------
-    def _init_params(self, seed: int) -> None:
+    def _init_params(self, flat: torch.Tensor, seed: int) -> None:
         """Reference initialisation (TH:69-78): N(0, 0.02) for Linear / Embedding weights, zero
         biases, LayerNorm (1, 0); MultiheadAttention.in_proj keeps xavier_uniform (not an nn.Linear)."""
         g = torch.Generator(device=self.device)
         g.manual_seed(seed)
-        for s in self.layout:
-            view = self.params[s.offset:s.offset + s.numel].view(s.shape)
-            n = s.name
+        for n in self.layout.state_dict_order():
+            s = self.layout[n]
+            view = flat[s.offset:s.offset + s.numel].view(s.shape)
             if n.endswith("ln_1.weight") or n.endswith("ln_2.weight") or n.endswith("ln_f.weight"):
                 view.fill_(1.0)
             elif n.endswith("bias"):
@@ -165,29 +184,99 @@ class NativeEngine:
             else:
                 view.copy_(torch.randn(s.shape, generator=g, device=self.device) * 0.02)
 
+    def _setup_sharded(self, full: torch.Tensor) -> None:
+        """FSDP / ZeRO-3 storage: this rank's partition of the matrix region (peer-visible), a
+        replicated copy of the vector tail, and staging buffers the gathers write into."""
+        Lt, dev, rank = self.layout, self.device, self.ctx.rank
+        S = Lt.big_shard_size
+        self.S = S
+        self.lo, self.hi = Lt.big_shard_range(rank)
+        self.shard_pb = self.comm.alloc("pshard", S, BF16)
+        self.shard_pb.tensor.copy_(full[self.lo:self.hi])
+        self.adj_table = self.comm.adjusted_table(self.shard_pb, S)
+        self.master = self.shard_pb.tensor.float()
+        b0, b1 = Lt.small_range()
+        self.small = full[b0:b1].clone()
+        self.master_small = self.small.float()
+        self.m_small = torch.zeros_like(self.master_small)
+        self.v_small = torch.zeros_like(self.master_small)
+        wte, wpe = Lt["transformer.wte.weight"], Lt["transformer.wpe.weight"]
+        self.stage_wte = torch.empty(wte.numel, dtype=BF16, device=dev)
+        self.stage_wpe = torch.empty(wpe.numel, dtype=BF16, device=dev)
+        # two staging buffers / flag arrays: GEMM k computes from slot k&1 while its gather warps
+        # prefetch the weight of GEMM k+1 into the other slot
+        self.stage_w = torch.empty(2, 4 * self.d * self.d, dtype=BF16, device=dev)
+        self.chunk_flags = torch.zeros(2, 1024, dtype=torch.int32, device=dev)
+        order = []
+        for l in range(self.L):
+            order += [f"transformer.h.{l}." + k for k in BIG_SUFFIXES]
+        for l in reversed(range(self.L)):
+            order += [f"transformer.h.{l}." + k for k in reversed(BIG_SUFFIXES)]
+        self._gorder = order
+        self._gseq = 0
+        self.gather_epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.params = None
+        self.P = {}
+        for s in Lt:
+            if s.offset >= b0:
+                self.P[s.name] = self.small[s.offset - b0:s.offset - b0 + s.numel].view(s.shape)
+            elif s.name == "transformer.wte.weight":
+                self.P[s.name] = self.stage_wte.view(s.shape)
+            elif s.name == "transformer.wpe.weight":
+                self.P[s.name] = self.stage_wpe.view(s.shape)
+            # block matrices have no resident view: _w() hands out the staging slot per GEMM
+
+    def _w(self, name: str):
+        """Weight matrix for the next GEMM: (tensor, K14 descriptor).  Resident weights: (P[name], None).
+        Sharded weights: the staging slot of this GEMM in the fixed per-micro-step order; the descriptor
+        tells the kernel whether to gather it itself (first GEMM only) and which weight to prefetch."""
+        if not self.sharded_params:
+            return self.P[name], None
+        k = self._gseq
+        self._gseq += 1
+        assert self._gorder[k] == name, (k, name, self._gorder[k])
+        s = self.layout[name]
+        slot = k & 1
+        desc = dict(table=self.adj_table, ws=self.ctx.world_size, flat_off=s.offset, shard=self.S,
+                    rows=s.shape[0], cols=s.shape[1], flags=self.chunk_flags[slot], epoch=self.gather_epoch,
+                    self_gather=1 if k == 0 else 0)
+        if k + 1 < len(self._gorder):
+            n = self.layout[self._gorder[k + 1]]
+            desc.update(pf_flat_off=n.offset, pf_rows=n.shape[0], pf_cols=n.shape[1],
+                        pf_stage=self.stage_w[1 - slot], pf_flags=self.chunk_flags[1 - slot])
+        return self.stage_w[slot][:s.numel].view(s.shape), desc
+
     # ---------------------------------------------------------------------------------------
     def _seed(self, layer: int, site: int) -> int:
-        # The per-step component lives in device memory (graph-replay safe): see ops.set_step_seed.
+        # The per-step component lives in device memory (graph-replay safe): see ops.step_seed_advance.
         return _mix(self.seed_base, layer, site)
 
     def _forward(self) -> None:
         o, P, p = self.ops, self.P, self.dropout
         B, T, d, H, hd = self.B, self.T, self.d, self.H, self.hd
+        if self.sharded_params:        # embedding tables: plain peer gather at the start of the micro-step
+            for name, stage in (("transformer.wte.weight", self.stage_wte), ("transformer.wpe.weight", self.stage_wpe)):
+                s = self.layout[name]
+                self.comm.gather_range(self.adj_table, stage, s.offset, s.numel, self.S)
         o.embedding_fwd(self.tokens, P["transformer.wte.weight"], P["transformer.wpe.weight"], self.x[0],
                         B, T, d, p, self._seed(-1, 0))
         for l in range(self.L):
             pre = f"transformer.h.{l}."
             st = self.stats[l]
             o.layernorm_fwd(self.x[l], P[pre + "ln_1.weight"], P[pre + "ln_1.bias"], self.ln1[l], st[0], st[1])
-            o.linear_fwd(self.ln1[l], P[pre + "attn.in_proj_weight"], self.qkv[l], bias=P[pre + "attn.in_proj_bias"])
+            w, g = self._w(pre + "attn.in_proj_weight")
+            o.linear_fwd(self.ln1[l], w, self.qkv[l], bias=P[pre + "attn.in_proj_bias"], gather=g)
             o.attention_fwd(self.qkv[l], self.att[l], self.lse[l], B, T, H, hd, self.causal, p, self._seed(l, 1))
-            o.linear_fwd(self.att[l], P[pre + "attn.out_proj.weight"], self.xmid[l],
-                         bias=P[pre + "attn.out_proj.bias"], epi=_ops.EPI_BIAS_RESID, aux=self.x[l])
+            w, g = self._w(pre + "attn.out_proj.weight")
+            o.linear_fwd(self.att[l], w, self.xmid[l], bias=P[pre + "attn.out_proj.bias"], epi=_ops.EPI_BIAS_RESID,
+                         aux=self.x[l], gather=g)
             o.layernorm_fwd(self.xmid[l], P[pre + "ln_2.weight"], P[pre + "ln_2.bias"], self.ln2[l], st[2], st[3])
-            o.linear_fwd(self.ln2[l], P[pre + "mlp.0.weight"], self.pre[l], bias=P[pre + "mlp.0.bias"],
-                         epi=_ops.EPI_BIAS_GELU, out2=self.act[l])
-            o.linear_fwd(self.act[l], P[pre + "mlp.2.weight"], self.x[l + 1], bias=P[pre + "mlp.2.bias"],
-                         epi=_ops.EPI_BIAS_RESID, aux=self.xmid[l], drop_p=p, seed=self._seed(l, 2))
+            w, g = self._w(pre + "mlp.0.weight")
+            o.linear_fwd(self.ln2[l], w, self.pre[l], bias=P[pre + "mlp.0.bias"], epi=_ops.EPI_BIAS_GELU,
+                         out2=self.act[l], gather=g)
+            w, g = self._w(pre + "mlp.2.weight")
+            o.linear_fwd(self.act[l], w, self.x[l + 1], bias=P[pre + "mlp.2.bias"], epi=_ops.EPI_BIAS_RESID,
+                         aux=self.xmid[l], drop_p=p, seed=self._seed(l, 2), gather=g)
         o.layernorm_fwd(self.x[self.L], P["transformer.ln_f.weight"], P["transformer.ln_f.bias"], self.lnf,
                         self.statf[0], self.statf[1])
         o.linear_fwd(self.lnf, P["transformer.wte.weight"], self.logits)
@@ -217,28 +306,32 @@ class NativeEngine:
                 dy = self.dy_drop
             o.colsum(dy, G[pre + "mlp.2.bias"], self.scratch, acc)
             o.linear_wgrad(dy, self.act[l], G[pre + "mlp.2.weight"], accumulate=acc)
-            o.linear_dgrad(dy, P[pre + "mlp.2.weight"], self.dbig, epi=_ops.EPI_DGELU, aux=self.pre[l])
+            w, g = self._w(pre + "mlp.2.weight")
+            o.linear_dgrad(dy, w, self.dbig, epi=_ops.EPI_DGELU, aux=self.pre[l], gather=g)
             o.colsum(self.dbig, G[pre + "mlp.0.bias"], self.scratch, acc)
             o.linear_wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc)
-            o.linear_dgrad(self.dbig, P[pre + "mlp.0.weight"], self.dln)
+            w, g = self._w(pre + "mlp.0.weight")
+            o.linear_dgrad(self.dbig, w, self.dln, gather=g)
             o.layernorm_bwd(self.dln, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid, dres=self.dres)
             o.layernorm_bwd_params(self.dln, self.xmid[l], st[2], st[3], G[pre + "ln_2.weight"],
                                    G[pre + "ln_2.bias"], self.scratch, acc)
             # ---- attention ----
             o.colsum(self.dmid, G[pre + "attn.out_proj.bias"], self.scratch, acc)
             o.linear_wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"], accumulate=acc)
-            o.linear_dgrad(self.dmid, P[pre + "attn.out_proj.weight"], self.datt)
+            w, g = self._w(pre + "attn.out_proj.weight")
+            o.linear_dgrad(self.dmid, w, self.datt, gather=g)
             o.attention_bwd(self.qkv[l], self.att[l], self.datt, self.lse[l], self.dqkv, self.attD, self.dq_acc,
                             B, T, H, hd, self.causal, p, self._seed(l, 1))
             o.colsum(self.dqkv, G[pre + "attn.in_proj_bias"], self.scratch, acc)
             o.linear_wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"], accumulate=acc)
-            o.linear_dgrad(self.dqkv, P[pre + "attn.in_proj_weight"], self.dln)
+            w, g = self._w(pre + "attn.in_proj_weight")
+            o.linear_dgrad(self.dqkv, w, self.dln, gather=g)
             o.layernorm_bwd(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres, dres=self.dmid)
             o.layernorm_bwd_params(self.dln, self.x[l], st[0], st[1], G[pre + "ln_1.weight"],
                                    G[pre + "ln_1.bias"], self.scratch, acc)
             if reduce_now:
-                # K13: this block's gradients are final -> all-reduce them on the comm stream while
-                # the compute stream continues with block l-1 (overlap with backward)
+                # K13: this block's matrix gradients are final -> all-reduce them on the comm stream
+                # while the compute stream continues with block l-1 (overlap with backward)
                 a, b = self.layout.layer_range(l)
                 self.comm.fork()
                 self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
@@ -254,6 +347,7 @@ class NativeEngine:
     def _micro_step(self, first_micro: bool, last_micro: bool) -> None:
         if self.dropout > 0:
             self.ops.step_seed_advance()      # new dropout masks every micro-step, also under graph replay
+        self._gseq = 0
         self._forward()
         self._loss_and_backward(first_micro, last_micro)
 
@@ -276,37 +370,55 @@ class NativeEngine:
             self._graphs[key] = g
         g.replay()
 
-    def _set_hp(self, grad_scale: float) -> None:
+    def _set_hp(self, grad_scale: float, hp: Optional[torch.Tensor] = None, advance: bool = True) -> None:
         c = self.cfg.optim
-        lr = warmup_lr(self.opt_step, c)
-        self.opt_step += 1
+        if advance:
+            self._lr = warmup_lr(self.opt_step, c)
+            self.opt_step += 1
         t = self.opt_step
         bc1 = 1.0 - c.beta1 ** t
         bc2 = 1.0 - c.beta2 ** t
-        self.ops.adamw_set_hp(self.hp, lr, c.beta1, c.beta2, c.eps, c.weight_decay, 1.0 / bc1,
-                              1.0 / math.sqrt(bc2), grad_scale, c.grad_clip)
+        self.ops.adamw_set_hp(self.hp if hp is None else hp, self._lr, c.beta1, c.beta2, c.eps, c.weight_decay,
+                              1.0 / bc1, 1.0 / math.sqrt(bc2), grad_scale, c.grad_clip)
+
+    def _boundary_fused(self, clip: bool) -> None:
+        ctx, ws, Lt = self.ctx, self.ctx.world_size, self.layout
+        if self.strategy == "ddp":          # gradients were all-reduced and scaled during backward (K13)
+            self._set_hp(1.0)
+            gn = None
+            if clip:
+                self.gnorm_sq.zero_()
+                self.ops.sumsq(self.grads, self.gnorm_sq, 1.0)
+                gn = self.gnorm_sq
+            self.ops.adamw_flat(self.master, self.exp_avg, self.exp_avg_sq, self.grads, self.params, self.hp, gn)
+            return
+        if not self.sharded_params:         # zero2: K15 over this rank's slice of the whole flat buffer
+            self._set_hp(1.0 / ws)
+            self.comm.rs_adamw(self.grads_pb, self.params_pb, self.lo, self.hi - self.lo, self.master,
+                               self.exp_avg, self.exp_avg_sq, self.grad_shard, self.hp, push_all=True)
+            return
+        # fsdp / zero3: vector tail replicated (K13 + local AdamW), matrix region partitioned (K15)
+        b0, b1 = Lt.small_range()
+        self.comm.allreduce(self.grads_pb, b0, b1 - b0, 1.0 / ws, side_stream=False)
+        extra = None
+        if clip:
+            self.gnorm_sq.zero_()
+            self.ops.sumsq(self.grads[b0:b1], self.gnorm_sq, 1.0)
+            extra = self.gnorm_sq
+        self._set_hp(1.0 / ws)
+        self._set_hp(1.0, hp=self.hp_small, advance=False)
+        self.comm.rs_adamw(self.grads_pb, self.shard_pb, self.lo, self.S, self.master, self.exp_avg,
+                           self.exp_avg_sq, self.grad_shard, self.hp, push_all=False, gnorm_out=self.gnorm2,
+                           extra_norm_sq=extra, weights_table=self.adj_table)
+        self.ops.adamw_flat(self.master_small, self.m_small, self.v_small, self.grads[b0:b1], self.small,
+                            self.hp_small, self.gnorm2[1:] if clip else None)
 
     def _optimizer_boundary(self) -> None:
         ctx, ws = self.ctx, self.ctx.world_size
         scale = 1.0 / ws
         clip = self.cfg.optim.grad_clip > 0
         if self.comm is not None:
-            if self.strategy == "ddp":          # gradients were all-reduced and scaled during backward (K13)
-                self._set_hp(1.0)
-                gn = None
-                if clip:
-                    self.gnorm_sq.zero_()
-                    self.ops.sumsq(self.grads, self.gnorm_sq, 1.0)
-                    gn = self.gnorm_sq
-                self.ops.adamw_flat(self.master, self.exp_avg, self.exp_avg_sq, self.grads, self.params, self.hp, gn)
-                return
-            # K15: pull + reduce my partition, clip, AdamW, store updated weights (to all ranks for ZeRO-2)
-            self._set_hp(scale)
-            self.comm.rs_adamw(self.grads_pb, self.params_pb, self.lo, self.hi - self.lo, self.master,
-                               self.exp_avg, self.exp_avg_sq, self.grad_shard, self.hp,
-                               push_all=(self.strategy == "zero2"))
-            if self.strategy in SHARDED_PARAMS:
-                ctx.all_gather(self.params[self.lo:self.hi], self.params)   # until K14 gathers per GEMM
+            self._boundary_fused(clip)
             return
         if self.strategy == "ddp":
             if ws > 1:
@@ -342,24 +454,45 @@ class NativeEngine:
         before = self.ops.launches
         self._run_micro(first, last)
         self.micro += 1
-        if self.micro % self.accum == 0:
+        if last:
             self._optimizer_boundary()
         eager = self.ops.launches - before
-        self._launches_per_step = eager + (getattr(self, "_graph_launches", 0) if self._graphs else 0)
+        self._launches_per_step = eager + (self._graph_launches if self._graphs else 0)
         return self.loss
 
     # ---------------------------------------------------------------------------------------
+    def _full_params(self) -> torch.Tensor:
+        if not self.sharded_params:
+            return self.params
+        Lt = self.layout
+        full = torch.empty(Lt.total, dtype=BF16, device=self.device)
+        self.ctx.all_gather(self.shard_pb.tensor, full[:Lt.big_end])
+        full[Lt.big_end:].copy_(self.small)
+        return full
+
     def state_dict(self) -> Dict[str, torch.Tensor]:
-        sd = {s.name: self.params[s.offset:s.offset + s.numel].view(s.shape).detach().clone().float()
-              for s in self.layout}
+        """Reference-keyed state_dict.  Collective for the parameter-sharded strategies."""
+        flat = self._full_params()
+        sd = {s.name: flat[s.offset:s.offset + s.numel].view(s.shape).detach().clone().float()
+              for s in (self.layout[n] for n in self.layout.state_dict_order())}
         sd["lm_head.weight"] = sd["transformer.wte.weight"]
         return sd
 
     def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        Lt = self.layout
         with torch.no_grad():
-            for s in self.layout:
-                self.params[s.offset:s.offset + s.numel].view(s.shape).copy_(sd[s.name])
-            self.master.copy_(self.params[self.lo:self.hi])
+            full = self.params if not self.sharded_params else torch.zeros(Lt.total, dtype=BF16, device=self.device)
+            for s in Lt:
+                full[s.offset:s.offset + s.numel].view(s.shape).copy_(sd[s.name])
+            if self.sharded_params:
+                self.shard_pb.tensor.copy_(full[self.lo:self.hi])
+                self.small.copy_(full[Lt.big_end:])
+                self.master_small.copy_(self.small)
+                self.m_small.zero_()
+                self.v_small.zero_()
+                self.master.copy_(self.shard_pb.tensor)
+            else:
+                self.master.copy_(self.params[self.lo:self.hi])
             self.exp_avg.zero_()
             self.exp_avg_sq.zero_()
 
@@ -372,4 +505,7 @@ class NativeEngine:
     def close(self) -> None:
         self._graphs.clear()
         if self.comm is not None:
+            self.P, self.G = {}, {}
+            self.grads = self.params = None
             self.comm.close()
+            self.comm = None

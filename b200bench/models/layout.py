@@ -1,7 +1,7 @@
 """Flat parameter layout shared by every strategy and by the native engine.
 
-All parameters of TinyGPT live in ONE flat buffer, in the reference's ``state_dict`` order
-(SURVEY.md §2.4).  The same offsets index the bf16 working weights, the bf16 gradient buffer and
+All parameters of TinyGPT live in ONE flat buffer: matrices first, vectors last (see
+``build_layout``); ``state_dict()`` still lists them in the reference's order.  The same offsets index the bf16 working weights, the bf16 gradient buffer and
 the fp32 master / Adam-moment buffers, so a rank's optimizer partition (ZeRO-2/3, FSDP) is simply
 a contiguous slice ``[rank*shard, (rank+1)*shard)`` and a DDP bucket is a contiguous range.
 
@@ -37,6 +37,7 @@ class ParamLayout:
         self.total = (end + quantum - 1) // quantum * quantum
         self.used = end
         self.world_size = max(1, world_size)
+        self.big_end = self.total
 
     # ---- sharding arithmetic -----------------------------------------------------------
     @property
@@ -60,9 +61,33 @@ class ParamLayout:
         return self.by_name[name]
 
     def layer_range(self, layer: int) -> Tuple[int, int]:
-        """Contiguous [start, end) of every tensor of one transformer block."""
+        """Contiguous [start, end) of the four weight matrices of one transformer block."""
         ss = [s for s in self.specs if s.layer == layer]
         return ss[0].offset, ss[-1].offset + ss[-1].numel
+
+    def small_range(self) -> Tuple[int, int]:
+        """The replicated tail: every LayerNorm vector and bias."""
+        return self.big_end, self.total
+
+    @property
+    def big_shard_size(self) -> int:
+        """Partition size when only the matrix region is sharded (FSDP / ZeRO-3)."""
+        return self.big_end // self.world_size
+
+    def big_shard_range(self, rank: int) -> Tuple[int, int]:
+        s = self.big_shard_size
+        return rank * s, (rank + 1) * s
+
+    def state_dict_order(self) -> List[str]:
+        """Tensor names in the reference's state_dict order, independent of the flat order."""
+        n_layer = 1 + max(s.layer for s in self.specs)
+        names = ["transformer.wte.weight", "transformer.wpe.weight"]
+        for i in range(n_layer):
+            p = f"transformer.h.{i}."
+            names += [p + k for k in ("ln_1.weight", "ln_1.bias", "attn.in_proj_weight", "attn.in_proj_bias",
+                                      "attn.out_proj.weight", "attn.out_proj.bias", "ln_2.weight", "ln_2.bias",
+                                      "mlp.0.weight", "mlp.0.bias", "mlp.2.weight", "mlp.2.bias")]
+        return names + ["transformer.ln_f.weight", "transformer.ln_f.bias"]
 
     def buckets(self, cap_elems: int) -> List[Tuple[int, int]]:
         """Contiguous gradient buckets of at most ``cap_elems`` elements, in REVERSE parameter
@@ -85,6 +110,12 @@ class ParamLayout:
 
 def build_layout(vocab_size: int, n_embd: int, n_head: int, n_layer: int, block_size: int,
                  world_size: int = 1, **_unused) -> ParamLayout:
+    """Flat order: every matrix first (embeddings, then per block in_proj / out_proj / fc1 / fc2),
+    then every vector (LayerNorm weights and biases, linear biases, final LayerNorm).  Keeping the
+    small tensors in one contiguous tail lets the parameter-sharding strategies treat them the way
+    DeepSpeed's ``stage3_param_persistence_threshold`` does (``configs/deepspeed/zero3.json:22``:
+    biases and LN vectors stay resident on every rank) with ONE replicated region instead of 130
+    scattered ones; the matrices in front of it are what gets partitioned."""
     d = n_embd
     specs: List[ParamSpec] = []
     off = 0
@@ -101,18 +132,26 @@ def build_layout(vocab_size: int, n_embd: int, n_head: int, n_layer: int, block_
     add("transformer.wpe.weight", (block_size, d), -1)
     for i in range(n_layer):
         p = f"transformer.h.{i}."
-        add(p + "ln_1.weight", (d,), i)
-        add(p + "ln_1.bias", (d,), i)
         add(p + "attn.in_proj_weight", (3 * d, d), i)
-        add(p + "attn.in_proj_bias", (3 * d,), i)
         add(p + "attn.out_proj.weight", (d, d), i)
-        add(p + "attn.out_proj.bias", (d,), i)
-        add(p + "ln_2.weight", (d,), i)
-        add(p + "ln_2.bias", (d,), i)
         add(p + "mlp.0.weight", (4 * d, d), i)
-        add(p + "mlp.0.bias", (4 * d,), i)
         add(p + "mlp.2.weight", (d, 4 * d), i)
-        add(p + "mlp.2.bias", (d,), i)
-    add("transformer.ln_f.weight", (d,), -2)
-    add("transformer.ln_f.bias", (d,), -2)
-    return ParamLayout(specs, world_size)
+    # the sharded ("big") region ends here, padded so that it splits evenly over the ranks
+    quantum = ALIGN * max(1, world_size)
+    off = (off + quantum - 1) // quantum * quantum
+    big_end = off
+    for i in range(n_layer):
+        p = f"transformer.h.{i}."
+        add(p + "ln_1.weight", (d,), -3)
+        add(p + "ln_1.bias", (d,), -3)
+        add(p + "attn.in_proj_bias", (3 * d,), -3)
+        add(p + "attn.out_proj.bias", (d,), -3)
+        add(p + "ln_2.weight", (d,), -3)
+        add(p + "ln_2.bias", (d,), -3)
+        add(p + "mlp.0.bias", (4 * d,), -3)
+        add(p + "mlp.2.bias", (d,), -3)
+    add("transformer.ln_f.weight", (d,), -3)
+    add("transformer.ln_f.bias", (d,), -3)
+    layout = ParamLayout(specs, world_size)
+    layout.big_end = big_end
+    return layout

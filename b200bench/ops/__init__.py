@@ -59,6 +59,9 @@ class NativeOps:
         L = self.lib
         vp, i, f, u, sz = c_void_p, c_int, c_float, c_uint, c_size_t
         L.b200_gemm_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp, vp, vp, f, u, i, i, vp]
+        ull = ctypes.c_ulonglong
+        L.b200_gemm_bf16_gather.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp, vp, vp, f, u, i, i, vp,
+                                            vp, i, ull, ull, i, i, vp, vp, i, ull, i, i, vp, vp]
         L.b200_attention_fwd.argtypes = [vp, vp, vp, i, i, i, i, i, f, u, vp]
         L.b200_attention_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, f, u, vp]
         L.b200_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i, i, f, vp]
@@ -84,28 +87,41 @@ class NativeOps:
 
     # ---- GEMM -------------------------------------------------------------------------------
     def gemm(self, A, B, D, M, N, K, a_mn=False, b_mn=False, epi=EPI_NONE, bias=None, aux=None, D2=None,
-             drop_p=0.0, seed=0, lda=None, ldb=None, ldd=None, bn=0, max_ctas=0) -> None:
+             drop_p=0.0, seed=0, lda=None, ldb=None, ldd=None, bn=0, max_ctas=0, gather=None) -> None:
         lda = lda or (M if a_mn else K)
         ldb = ldb or (N if b_mn else K)
         ldd = ldd or N
+        if gather is not None:
+            # K14: B is a staging buffer filled by the kernel itself from the owners' partitions
+            g = gather
+            self._ck(self.lib.b200_gemm_bf16_gather(_p(A), _p(B), _p(D), M, N, K, lda, ldb, ldd, int(a_mn),
+                                                    int(b_mn), epi, _p(bias), _p(aux), _p(D2), drop_p, seed, bn,
+                                                    max_ctas, _stream(), g["table"], g["ws"], g["flat_off"],
+                                                    g["shard"], g["rows"], g["cols"], _p(g["flags"]),
+                                                    _p(g["epoch"]), int(g.get("self_gather", 1)),
+                                                    g.get("pf_flat_off", 0), g.get("pf_rows", 0),
+                                                    g.get("pf_cols", 0), _p(g.get("pf_stage")),
+                                                    _p(g.get("pf_flags"))), "gemm_gather")
+            self.launches += 2
+            return
         self._ck(self.lib.b200_gemm_bf16(_p(A), _p(B), _p(D), M, N, K, lda, ldb, ldd, int(a_mn), int(b_mn),
                                          epi, _p(bias), _p(aux), _p(D2), drop_p, seed, bn, max_ctas,
                                          _stream()), "gemm")
         self.launches += 1
 
-    def linear_fwd(self, x, w, out, bias=None, epi=None, aux=None, out2=None, drop_p=0.0, seed=0) -> None:
+    def linear_fwd(self, x, w, out, bias=None, epi=None, aux=None, out2=None, drop_p=0.0, seed=0, gather=None) -> None:
         """out[M,N] = epi(x[M,K] @ w[N,K]^T)"""
         M, K = x.shape
         N = w.shape[0]
         if epi is None:
             epi = EPI_BIAS if bias is not None else EPI_NONE
-        self.gemm(x, w, out, M, N, K, epi=epi, bias=bias, aux=aux, D2=out2, drop_p=drop_p, seed=seed)
+        self.gemm(x, w, out, M, N, K, epi=epi, bias=bias, aux=aux, D2=out2, drop_p=drop_p, seed=seed, gather=gather)
 
-    def linear_dgrad(self, dy, w, dx, epi=EPI_NONE, aux=None) -> None:
+    def linear_dgrad(self, dy, w, dx, epi=EPI_NONE, aux=None, gather=None) -> None:
         """dx[M,K] = epi(dy[M,N] @ w[N,K])"""
         M, N = dy.shape
         K = w.shape[1]
-        self.gemm(dy, w, dx, M, K, N, b_mn=True, epi=epi, aux=aux)
+        self.gemm(dy, w, dx, M, K, N, b_mn=True, epi=epi, aux=aux, gather=gather)
 
     def linear_wgrad(self, dy, x, dw, accumulate=False) -> None:
         """dw[N,K] (+)= dy[M,N]^T @ x[M,K]"""

@@ -54,7 +54,8 @@ class PeerComm:
         L.b200_peer_free.argtypes = [vp]
         L.b200_comm_flag_bytes.restype = sz
         L.b200_comm_allreduce.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
-        L.b200_comm_rs_adamw.argtypes = [vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, i, vp]
+        L.b200_comm_rs_adamw.argtypes = [vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
+        L.b200_comm_gather_range.argtypes = [vp, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_ulonglong, i, vp]
         L.b200_comm_push_ranges.argtypes = [vp, vp, i, i, vp, i, vp]
         L.b200_peer_copy.argtypes = [vp, vp, sz, i, vp]
         self.buffers: Dict[str, PeerBuffer] = {}
@@ -119,12 +120,13 @@ class PeerComm:
         self.ops.launches += 2
 
     def rs_adamw(self, grads: PeerBuffer, weights: PeerBuffer, lo: int, n: int, master, m, v, gshard, hp,
-                 push_all: bool, gnorm_out=None, ctas: int = 128) -> None:
+                 push_all: bool, gnorm_out=None, extra_norm_sq=None, ctas: int = 128, weights_table=None) -> None:
         s = torch.cuda.current_stream()
         p = lambda t: c_void_p(t.data_ptr()) if t is not None else c_void_p(0)  # noqa: E731
-        rc = self.ops.lib.b200_comm_rs_adamw(grads.table, weights.table, self.flags.table, self.rank, self.ws,
+        wt = weights_table if weights_table is not None else weights.table
+        rc = self.ops.lib.b200_comm_rs_adamw(grads.table, wt, self.flags.table, self.rank, self.ws,
                                              lo, n, p(master), p(m), p(v), p(gshard), p(hp), int(push_all),
-                                             p(gnorm_out), ctas, c_void_p(s.cuda_stream))
+                                             p(gnorm_out), p(extra_norm_sq), ctas, c_void_p(s.cuda_stream))
         if rc:
             raise _ops.NativeError(f"comm_rs_adamw failed with code {rc}")
         self.ops.launches += 2
@@ -137,6 +139,19 @@ class PeerComm:
         if rc:
             raise _ops.NativeError(f"comm_push_ranges failed with code {rc}")
         self.ops.launches += 2
+
+    def adjusted_table(self, buf: PeerBuffer, shard_elems: int, elem_size: int = 2):
+        """Pointer table for a partition buffer, biased so that FLAT offsets index it: entry r =
+        (rank r's partition base) - r * shard_elems."""
+        return (c_void_p * self.ws)(*[pp - r * shard_elems * elem_size for r, pp in enumerate(buf.peer_ptrs)])
+
+    def gather_range(self, table, dst: torch.Tensor, flat_off: int, n: int, shard_elems: int, ctas: int = 128) -> None:
+        rc = self.ops.lib.b200_comm_gather_range(table, self.ws, c_void_p(dst.data_ptr()), flat_off, n,
+                                                 shard_elems, ctas,
+                                                 c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc:
+            raise _ops.NativeError(f"comm_gather_range failed with code {rc}")
+        self.ops.launches += 1
 
     def peer_copy(self, src_ptr: int, dst: torch.Tensor, nbytes: int, ctas: int = 64) -> None:
         rc = self.ops.lib.b200_peer_copy(c_void_p(src_ptr), c_void_p(dst.data_ptr()), nbytes, ctas,

@@ -127,7 +127,7 @@ class TorchEngine:
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
         flat = self._full_params()
-        sd = {s.name: flat[s.offset:s.offset + s.numel].view(s.shape).detach().clone() for s in self.layout}
+        sd = {s.name: flat[s.offset:s.offset + s.numel].view(s.shape).detach().clone() for s in (self.layout[n] for n in self.layout.state_dict_order())}
         sd["lm_head.weight"] = sd["transformer.wte.weight"]
         return sd
 

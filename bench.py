@@ -58,7 +58,18 @@ def run_reference(a: argparse.Namespace) -> None:
            "--warmup-steps", str(a.warmup), "--per-device-batch", str(BATCH), "--grad-accum", str(GRAD_ACCUM),
            "--results-dir", outdir]
     t0 = time.time()
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    # torchrun exports TORCHELASTIC_USE_AGENT_STORE=True; with it c10d's tcp:// rendezvous makes EVERY rank a
+    # store client and the reference (which hosts its own store on rank 0, TH:190-195) waits forever.
+    env = {k: v for k, v in os.environ.items() if not k.startswith(("TORCHELASTIC", "TORCH_NCCL", "NCCL_ASYNC"))}
+    env["OMP_NUM_THREADS"] = "8"          # torchrun pins it to 1, which makes the reference's CPU-side init crawl
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=a.ref_timeout)
+    except subprocess.TimeoutExpired as te:
+        if rank == 0:
+            tail = ((te.stdout or b"")[-300:]).decode("utf-8", "replace").replace("\n", " | ") if te.stdout else ""
+            emit({"impl": "reference", "unavailable": f"reference harness did not finish within {a.ref_timeout}s "
+                  f"at world size {ws}; last output: {tail}"})
+        return
     wall = time.time() - t0
     if rank != 0:
         return
@@ -126,7 +137,10 @@ def run_native(a: argparse.Namespace) -> None:
 
     # ---- warm-up (untimed): builds tensor maps, captures the CUDA graph -----------------------
     resident = [src.next() for _ in range(8)]            # device-resident batches for the kernel-only arm
-    for i in range(max(3, a.warmup)):
+    # warm-up must cover every micro-step variant of an accumulation cycle twice (eager, then graph capture)
+    n_warm = max(3, a.warmup, 2 * eng.accum + 2 if eng.accum > 1 else 0)
+    n_warm += (-n_warm) % eng.accum          # stop on an accumulation boundary
+    for i in range(n_warm):
         eng.train_step(resident[i % 8], resident[i % 8])
     sync_all()
 
@@ -171,7 +185,7 @@ def run_native(a: argparse.Namespace) -> None:
         per_step = eng.kernel_launches_per_step()
         emit({
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": ws, "steps": a.steps,
-            "warmup": max(3, a.warmup), "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
+            "warmup": n_warm, "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": (value / PUBLISHED_DDP[ws]) if ws in PUBLISHED_DDP else None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"model": f"TinyGPT tier {a.tier} ({eng.layout.num_params()/1e6:.1f}M)",
@@ -206,6 +220,7 @@ def main() -> None:
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--dropout", type=float, default=0.1)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--ref-timeout", type=float, default=180.0, help="seconds before the reference arm is abandoned")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)

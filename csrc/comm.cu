@@ -193,7 +193,8 @@ struct RsAdamParams {
   size_t lo, n;
   int rank;
   int push_all;       // 1: store updated weights to every rank (ZeRO-2); 0: own copy only
-  float* gnorm_out;   // optional: global grad norm (for logging)
+  float* gnorm_out;   // optional: [0] = global grad norm, [1] = its square
+  const float* extra_norm_sq;  // optional: squared norm of gradients handled outside this kernel
 };
 
 __device__ __forceinline__ void adam8(float* master, float* m, float* v, size_t i8,
@@ -296,9 +297,13 @@ rs_adamw_kernel(const RsAdamParams p) {
     float tot = 0.f;
 #pragma unroll
     for (int r = 0; r < WS; ++r) tot += *reinterpret_cast<volatile float*>(norm_local + r);
+    if (p.extra_norm_sq) tot += *p.extra_norm_sq;
     const float norm = sqrtf(tot);
     if (norm > clip) gscale *= clip / (norm + 1e-6f);
-    if (p.gnorm_out && blockIdx.x == 0 && threadIdx.x == 0) *p.gnorm_out = norm;
+    if (p.gnorm_out && blockIdx.x == 0 && threadIdx.x == 0) {
+      p.gnorm_out[0] = norm;
+      p.gnorm_out[1] = tot;
+    }
   }
 
   // ---- phase 2 (or the only phase): AdamW on the partition, push bf16 weights ----------------
@@ -405,6 +410,33 @@ peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t 
   }
 }
 
+// Pull the flat range [flat_off, flat_off+n) from the owners' partitions into a local buffer
+// (embedding tables at the start of a ZeRO-3 / FSDP step; the per-layer weights are gathered inside
+// their GEMMs instead, see gemm_sm100.cu K14).  src[r] is rank r's partition base minus r*shard.
+__global__ void __launch_bounds__(COMM_THREADS, 2)
+gather_range_kernel(PeerPtrs src, __nv_bfloat16* __restrict__ dst, unsigned long long flat_off,
+                    unsigned long long n, unsigned long long shard) {
+  const size_t nvec = n >> 3;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i0 = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += 4 * stride) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < nvec) {
+        const size_t flat = flat_off + i * 8;
+        const int owner = static_cast<int>(flat / shard);
+        v[u] = ld_peer_v4(static_cast<const __nv_bfloat16*>(src.p[owner]) + flat);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < nvec) reinterpret_cast<uint4*>(dst)[i] = v[u];
+    }
+  }
+}
+
 static PeerPtrs make_ptrs(void* const* arr, int ws) {
   PeerPtrs p;
   for (int i = 0; i < MAX_RANKS; ++i) p.p[i] = i < ws ? arr[i] : nullptr;
@@ -462,7 +494,8 @@ extern "C" int b200_comm_allreduce(void* const* grads, void* const* flags, int r
 extern "C" int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* flags,
                                   int rank, int ws, size_t lo, size_t n, float* master, float* m,
                                   float* v, void* gshard, const float* hp, int push_all,
-                                  float* gnorm_out, int ctas, void* stream) {
+                                  float* gnorm_out, const float* extra_norm_sq, int ctas,
+                                  void* stream) {
   if (n % 8 || lo % 8) return -2;
   if (ctas < 1) ctas = 64;
   if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
@@ -481,6 +514,7 @@ extern "C" int b200_comm_rs_adamw(void* const* grads, void* const* weights, void
   p.rank = rank;
   p.push_all = push_all;
   p.gnorm_out = gnorm_out;
+  p.extra_norm_sq = extra_norm_sq;
   DISPATCH_WS(ws, (rs_adamw_kernel<W><<<ctas, COMM_THREADS, 0, s>>>(p)));
   comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 1);
   return static_cast<int>(cudaGetLastError());
@@ -494,6 +528,15 @@ extern "C" int b200_comm_push_ranges(void* const* weights, void* const* flags, i
   if (ctas < 1) ctas = 1;
   DISPATCH_WS(ws, (peer_push_ranges_kernel<W><<<ctas, 256, 0, s>>>(w, f, rank, ranges_dev, n_ranges)));
   comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 2);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst,
+                                      unsigned long long flat_off, unsigned long long n,
+                                      unsigned long long shard_elems, int ctas, void* stream) {
+  if (n % 8 || flat_off % 8 || shard_elems % 8 || ws > MAX_RANKS) return -2;
+  gather_range_kernel<<<ctas > 0 ? ctas : 128, COMM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      make_ptrs(shard_adj, ws), static_cast<__nv_bfloat16*>(dst), flat_off, n, shard_elems);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -31,6 +31,28 @@ namespace b200 {
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
 constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_GATHER_THREADS = 128;   // 4 extra warps in gather mode
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u32(uint32_t* addr, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* addr) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(addr)
+               : "memory");
+  return v;
+}
+// generic-proxy global writes/reads <-> async-proxy (TMA) accesses of the same global memory
+__device__ __forceinline__ void fence_proxy_async_global() {
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
 
 template <int BN>
 struct GemmCfg {
@@ -57,10 +79,30 @@ struct GemmParams {
   uint32_t drop_seed;
   const uint32_t* seed_ptr;     // per-step seed word in device memory (nullable)
   int num_m_tiles, num_n_tiles;
+  // ---- K14: all-gather of the B operand fused into this GEMM (gather_ws == 0: off) -------------
+  // B (a weight matrix, row-major [g_rows, g_cols]) is partitioned over ranks by flat offset; four
+  // extra warps per CTA pull it chunk by chunk (g_chunk_rows rows each) from the owners' shards over
+  // NVLink into the local staging buffer that the TMA descriptor of B points at, and publish one flag
+  // per chunk; the TMA producer waits for the chunks a tile needs.  Transfer overlaps the math.
+  int gather_ws;
+  int g_rows, g_cols, g_chunk_rows;
+  unsigned long long g_flat_off;     // flat-layout offset of B[0,0]
+  unsigned long long g_shard;        // elements per rank partition
+  const __nv_bfloat16* g_src[8];     // per rank: partition base MINUS rank*g_shard (flat-indexed)
+  __nv_bfloat16* g_dst;              // staging buffer (== B)
+  uint32_t* g_flags;                 // [chunks] ready flags
+  const uint32_t* g_epoch;           // device word E, bumped after every gather-GEMM
+  int g_self;                        // 1: gather B in this kernel (flags <- E+1); 0: a previous kernel prefetched it
+  // prefetch job: the NEXT GEMM's weight, pulled into its staging buffer while this GEMM computes
+  // (flags <- E+2).  pf_rows == 0: none.   [FSDP forward_prefetch / backward_prefetch]
+  int pf_rows, pf_cols;
+  unsigned long long pf_flat_off;
+  __nv_bfloat16* pf_dst;
+  uint32_t* pf_flags;
 };
 
 template <int BN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS + GEMM_GATHER_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                          const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
@@ -107,10 +149,32 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      const bool gather = p.gather_ws > 0;
+      // own weight: published as E+1 either by this kernel's gather warps or by the previous kernel's
+      // prefetch (whose epoch was E-1).  Zero-filled flags can never satisfy the wait.
+      const uint32_t g_want = gather ? *p.g_epoch + 1u : 0u;
+      bool g_all_ready = false;
+      auto wait_chunk = [&](int c) {
+        uint32_t spins = 0;
+        while (static_cast<int32_t>(ld_acquire_gpu_u32(p.g_flags + c) - g_want) < 0) {
+          if (++spins > (1u << 28)) __trap();
+        }
+      };
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
         const int n0 = (tile / p.num_m_tiles) * BN;
+        if (gather && !p.b_mn) {   // B rows = n: this tile needs the chunks covering [n0, n0+BN)
+          const int n1 = (n0 + BN < p.g_rows ? n0 + BN : p.g_rows) - 1;
+          for (int c = n0 / p.g_chunk_rows; c <= n1 / p.g_chunk_rows; ++c) wait_chunk(c);
+          fence_proxy_async_global();
+        }
         for (int kb = 0; kb < num_kb; ++kb) {
+          if (gather && p.b_mn && !g_all_ready) {   // B rows = k: one chunk per k-block, first tile only
+            const int r0 = kb * GEMM_BK;
+            const int r1 = (r0 + GEMM_BK < p.g_rows ? r0 + GEMM_BK : p.g_rows) - 1;
+            for (int c = r0 / p.g_chunk_rows; c <= r1 / p.g_chunk_rows; ++c) wait_chunk(c);
+            fence_proxy_async_global();
+          }
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = tiles + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
@@ -135,7 +199,50 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             phase ^= 1;
           }
         }
+        g_all_ready = true;
       }
+    }
+  } else if (warp >= 6) {
+    // ================================ K14 gather warps =============================
+    if (p.gather_ws > 0) {
+      const int gt = threadIdx.x - GEMM_THREADS;   // 0..127
+      const uint32_t E = *p.g_epoch;
+      auto gather_job = [&](unsigned long long flat_off, int rows, int cols, __nv_bfloat16* out,
+                            uint32_t* flags, uint32_t publish) {
+        const size_t chunk_elems = static_cast<size_t>(p.g_chunk_rows) * cols;
+        const size_t total = static_cast<size_t>(rows) * cols;
+        const int nchunks = (rows + p.g_chunk_rows - 1) / p.g_chunk_rows;
+        for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+          size_t e = c * chunk_elems;
+          const size_t e1 = (e + chunk_elems < total) ? e + chunk_elems : total;
+          while (e < e1) {
+            const size_t flat = flat_off + e;
+            const int owner = static_cast<int>(flat / p.g_shard);
+            const size_t seg_end = static_cast<size_t>(owner + 1) * p.g_shard - flat_off;
+            const size_t e_stop = seg_end < e1 ? seg_end : e1;
+            const uint4* src = reinterpret_cast<const uint4*>(p.g_src[owner] + flat);
+            uint4* dst = reinterpret_cast<uint4*>(out + e);
+            const size_t nvec = (e_stop - e) >> 3;
+            // 8 independent 16-byte loads per thread in flight: NVLink latency is hidden by depth
+            for (size_t i = gt; i < nvec; i += 8 * GEMM_GATHER_THREADS) {
+              uint4 v[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u)
+                if (i + u * GEMM_GATHER_THREADS < nvec) v[u] = ld_volatile_v4(src + i + u * GEMM_GATHER_THREADS);
+#pragma unroll
+              for (int u = 0; u < 8; ++u)
+                if (i + u * GEMM_GATHER_THREADS < nvec) dst[i + u * GEMM_GATHER_THREADS] = v[u];
+            }
+            e = e_stop;
+          }
+          __threadfence();
+          fence_proxy_async_global();
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          if (gt == 0) st_release_gpu_u32(flags + c, publish);
+        }
+      };
+      if (p.g_self) gather_job(p.g_flat_off, p.g_rows, p.g_cols, p.g_dst, p.g_flags, E + 1u);  // urgent: this GEMM waits on it
+      if (p.pf_rows > 0) gather_job(p.pf_flat_off, p.pf_rows, p.pf_cols, p.pf_dst, p.pf_flags, E + 2u);
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
@@ -179,7 +286,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         }
       }
     }
-  } else {
+  } else if (warp < 6) {
     // ================================ epilogue ====================================
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
     const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
@@ -369,7 +476,8 @@ static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams&
   int grid = device_sm_count();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (tiles < grid) grid = tiles;
-  gemm_bf16_tcgen05_kernel<BN><<<grid, GEMM_THREADS, Cfg::kSmemBytes, stream>>>(ma, mb, p);
+  const int threads = GEMM_THREADS + (p.gather_ws > 0 ? GEMM_GATHER_THREADS : 0);
+  gemm_bf16_tcgen05_kernel<BN><<<grid, threads, Cfg::kSmemBytes, stream>>>(ma, mb, p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -377,10 +485,26 @@ static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams&
 
 using namespace b200;
 
-extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int lda,
-                              int ldb, int ldd, int a_mn, int b_mn, int epi, const void* bias,
-                              const void* aux, void* D2, float drop_p, unsigned int drop_seed,
-                              int bn_hint, int max_ctas, void* stream) {
+struct GatherArgs {
+  int ws = 0;
+  const void* const* shard_adj = nullptr;
+  unsigned long long flat_off = 0, shard = 0;
+  int rows = 0, cols = 0;
+  void* flags = nullptr;
+  void* epoch = nullptr;
+  int self_gather = 1;
+  unsigned long long pf_flat_off = 0;
+  int pf_rows = 0, pf_cols = 0;
+  void* pf_dst = nullptr;
+  void* pf_flags = nullptr;
+};
+
+__global__ void gather_epoch_bump_kernel(uint32_t* w) { *w += 1; }
+
+static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K, int lda, int ldb,
+                     int ldd, int a_mn, int b_mn, int epi, const void* bias, const void* aux,
+                     void* D2, float drop_p, unsigned int drop_seed, int bn_hint, int max_ctas,
+                     void* stream, const GatherArgs& ga) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if ((N % 8) || (K % 8) || (lda % 8) || (ldb % 8) || (ldd % 8)) return -2;
   if (a_mn && (M % 8)) return -2;
@@ -429,7 +553,72 @@ extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int 
   }
   p.drop_seed = drop_seed;
   p.seed_ptr = step_seed_ptr();
+  p.gather_ws = ga.ws;
+  if (ga.ws > 0) {
+    if (ga.ws > 8 || ldb != ga.cols || (ga.cols % 8) || (ga.flat_off % 8) || (ga.shard % 8)) return -2;
+    p.g_rows = ga.rows;
+    p.g_cols = ga.cols;
+    p.g_chunk_rows = 32;   // small chunks: every CTA's gather warps get work, flags stay fine-grained
+    p.g_flat_off = ga.flat_off;
+    p.g_shard = ga.shard;
+    for (int r = 0; r < 8; ++r)
+      p.g_src[r] = r < ga.ws ? static_cast<const __nv_bfloat16*>(ga.shard_adj[r]) : nullptr;
+    p.g_dst = static_cast<__nv_bfloat16*>(const_cast<void*>(B));
+    p.g_flags = static_cast<uint32_t*>(ga.flags);
+    p.g_epoch = static_cast<const uint32_t*>(ga.epoch);
+    p.g_self = ga.self_gather;
+    p.pf_rows = ga.pf_rows;
+    p.pf_cols = ga.pf_cols;
+    p.pf_flat_off = ga.pf_flat_off;
+    p.pf_dst = static_cast<__nv_bfloat16*>(ga.pf_dst);
+    p.pf_flags = static_cast<uint32_t*>(ga.pf_flags);
+    if (ga.pf_rows > 0 && ((ga.pf_cols % 8) || (ga.pf_flat_off % 8) || (ga.pf_rows + 31) / 32 > 1024)) return -2;
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (BN == 256) return launch_gemm<256>(ma, mb, p, max_ctas, s);
-  return launch_gemm<128>(ma, mb, p, max_ctas, s);
+  int rc2 = (BN == 256) ? launch_gemm<256>(ma, mb, p, max_ctas, s) : launch_gemm<128>(ma, mb, p, max_ctas, s);
+  if (rc2 == 0 && ga.ws > 0) {
+    gather_epoch_bump_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(ga.epoch));
+    rc2 = static_cast<int>(cudaGetLastError());
+  }
+  return rc2;
+}
+
+extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int lda,
+                              int ldb, int ldd, int a_mn, int b_mn, int epi, const void* bias,
+                              const void* aux, void* D2, float drop_p, unsigned int drop_seed,
+                              int bn_hint, int max_ctas, void* stream) {
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, epi, bias, aux, D2, drop_p, drop_seed,
+                   bn_hint, max_ctas, stream, GatherArgs());
+}
+
+// K14: same GEMM, but B (a weight matrix of `rows` x `cols`, partitioned over `ws` ranks by flat
+// offset) is first pulled from the owners' shards into `B_staging` by extra warps of the SAME kernel,
+// chunk by chunk, while the tensor cores already work on the chunks that have arrived.
+extern "C" int b200_gemm_bf16_gather(const void* A, void* B_staging, void* D, int M, int N, int K,
+                                     int lda, int ldb, int ldd, int a_mn, int b_mn, int epi,
+                                     const void* bias, const void* aux, void* D2, float drop_p,
+                                     unsigned int drop_seed, int bn_hint, int max_ctas, void* stream,
+                                     const void* const* shard_adj, int ws,
+                                     unsigned long long flat_off, unsigned long long shard_elems,
+                                     int rows, int cols, void* chunk_flags, void* epoch_word,
+                                     int self_gather, unsigned long long pf_flat_off, int pf_rows,
+                                     int pf_cols, void* pf_staging, void* pf_flags) {
+  GatherArgs ga;
+  ga.self_gather = self_gather;
+  ga.pf_flat_off = pf_flat_off;
+  ga.pf_rows = pf_rows;
+  ga.pf_cols = pf_cols;
+  ga.pf_dst = pf_staging;
+  ga.pf_flags = pf_flags;
+  ga.ws = ws;
+  ga.shard_adj = shard_adj;
+  ga.flat_off = flat_off;
+  ga.shard = shard_elems;
+  ga.rows = rows;
+  ga.cols = cols;
+  ga.flags = chunk_flags;
+  ga.epoch = epoch_word;
+  if ((rows + 31) / 32 > 1024) return -3;   // chunk_flags holds 1024 words
+  return gemm_impl(A, B_staging, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, epi, bias, aux, D2, drop_p,
+                   drop_seed, bn_hint, max_ctas, stream, ga);
 }

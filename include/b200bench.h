@@ -109,10 +109,34 @@ int b200_comm_allreduce(void* const* grads, void* const* flags, int rank, int ws
                         size_t n, float scale, int ctas, void* stream);
 /* K15: this rank's partition [lo, lo+n): g = sum over ranks of grads; optional global-norm clip
  * (hp[8]); AdamW on fp32 master/m/v; bf16 weights stored to every rank (push_all=1, ZeRO-2) or to
- * the own buffer only (ZeRO-3 / FSDP).  gshard: n bf16 of local scratch. hp as in b200_adamw. */
+ * the own buffer only (ZeRO-3 / FSDP).  gshard: n bf16 of local scratch. hp as in b200_adamw.
+ * gnorm_out (nullable, 2 floats): norm and squared norm; extra_norm_sq (nullable): squared norm of
+ * gradients that are updated outside this kernel (the replicated small tensors under ZeRO-3). */
 int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* flags, int rank,
                        int ws, size_t lo, size_t n, float* master, float* m, float* v, void* gshard,
-                       const float* hp, int push_all, float* gnorm_out, int ctas, void* stream);
+                       const float* hp, int push_all, float* gnorm_out, const float* extra_norm_sq,
+                       int ctas, void* stream);
+/* K14: the GEMM of b200_gemm_bf16 with the all-gather of its B operand fused in.  B is a weight
+ * matrix [rows, cols] partitioned over ws ranks by flat offset (partition size shard_elems, B[0,0] at
+ * flat_off); shard_adj[r] = rank r's partition base MINUS r*shard_elems elements, as mapped here.
+ * Four extra warps per CTA pull 32-row chunks into B_staging and publish chunk_flags (1024 words,
+ * zero-filled once); the TMA producer waits per chunk.  epoch_word: device uint32, zero-filled once.
+ * self_gather=0 means an earlier call already prefetched B into B_staging; pf_* (pf_rows=0: none)
+ * names the NEXT call's weight, which this kernel pulls into pf_staging / pf_flags while it computes
+ * (use two staging buffers and two flag arrays alternately).
+ * Replaces FSDP's pre-forward all-gather / ZeRO-3's per-module gathers (TH:231-237,366; SURVEY N4,N8). */
+int b200_gemm_bf16_gather(const void* A, void* B_staging, void* D, int M, int N, int K, int lda,
+                          int ldb, int ldd, int a_mn, int b_mn, int epi, const void* bias,
+                          const void* aux, void* D2, float drop_p, unsigned int drop_seed, int bn_hint,
+                          int max_ctas, void* stream, const void* const* shard_adj, int ws,
+                          unsigned long long flat_off, unsigned long long shard_elems, int rows,
+                          int cols, void* chunk_flags, void* epoch_word, int self_gather,
+                          unsigned long long pf_flat_off, int pf_rows, int pf_cols, void* pf_staging,
+                          void* pf_flags);
+/* Plain gather of the flat range [flat_off, flat_off+n) from the owners' partitions into dst. */
+int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst, unsigned long long flat_off,
+                           unsigned long long n, unsigned long long shard_elems, int ctas,
+                           void* stream);
 /* Copies owned small ranges (device array of (offset, length) pairs, elements) to every peer. */
 int b200_comm_push_ranges(void* const* weights, void* const* flags, int rank, int ws,
                           const long long* ranges_dev, int n_ranges, void* stream);
