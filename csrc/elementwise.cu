@@ -12,6 +12,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "b200_internal.h"
 #include "sm100_ptx.cuh"
@@ -796,5 +797,77 @@ extern "C" int b200_step_seed_advance(void* stream) {
   if (!g_step_seed_ptr) return -6;
   bump_step_seed_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(
       const_cast<uint32_t*>(g_step_seed_ptr));
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ----------------------------------------------------------------------------------------------
+// b200_colsum_static: the bias-gradient column sum for callers that must not allocate.
+//
+// b200_colsum needs a scratch buffer (fp32 partial sums + completion counters) that the caller has to
+// obtain from somewhere.  Some callers have nowhere to get it: a C plug-in running inside a host
+// framework whose memory pool already owns almost all of HBM (a fresh cudaMalloc there either fails
+// or fragments the pool), or a step loop that may not touch the CUDA allocator at all because
+// cudaMalloc/cudaFree take driver-wide locks and synchronise the device.  For them the scratch lives
+// in a file-scope device array that is part of the library image: every GPU that loads the library
+// holds kStaticScratchBytes (512 KiB) of it until the process exits, and nothing is ever allocated or
+// freed by this entry point (no cudaMalloc, no cudaFree, no library routine that allocates).
+//
+// In host code the name of a __device__ array is only a host-side stand-in for the symbol, not a
+// device address, so it cannot be handed to a kernel; the address is looked up with
+// cudaGetSymbolAddress once per device, with that device current, on the FIRST call made on that
+// device.  Make that first call before any stream capture starts.
+//
+// The array is shared by every call and keeps whatever the previous call left in it.  The completion
+// counters at its head must be zero when the kernel starts, so they are cleared on the caller's
+// stream before every launch; the partial sums need no clearing (every slot that is read is written
+// first).  Because there is only one array per GPU, two calls whose kernels overlap on the same GPU
+// (different streams, or different host threads) race on it: keep calls on one device stream-ordered.
+// Shapes beyond the built-in buffer (more than 65536 columns, or more than kStaticScratchBytes of
+// partials) are rejected with B200_ERR_STATIC_SCRATCH and a message on stderr; use b200_colsum with
+// your own buffer for those.
+// ----------------------------------------------------------------------------------------------
+namespace b200 {
+constexpr size_t kStaticScratchBytes = 512u << 10;  // 512 KiB per GPU: enough for any N <= 65536
+static __device__ __align__(256) unsigned char g_colsum_static_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+static void* g_static_scratch_addr[kMaxDevices] = {nullptr};
+}  // namespace b200
+
+extern "C" size_t b200_colsum_static_max_bytes(void) { return b200::kStaticScratchBytes; }
+
+extern "C" int b200_colsum_static(const void* dy, void* out, int M, int N, int ld, int accumulate,
+                                  void* stream) {
+  if (M <= 0 || N <= 0) return 0;
+  if ((N % 8) || (ld % 8)) return -2;
+  const size_t need = b200_colreduce_scratch_bytes(M, N, 1);
+  if ((N + 255) / 256 > kColreduceCounters || need > kStaticScratchBytes) {
+    fprintf(stderr,
+            "b200_colsum_static: M=%d N=%d is beyond the built-in scratch (at most %d columns and %zu "
+            "bytes; this shape needs %zu bytes); call b200_colsum with a caller-provided buffer\n",
+            M, N, kColreduceCounters * 256, static_cast<size_t>(kStaticScratchBytes), need);
+    return B200_ERR_STATIC_SCRATCH;
+  }
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= kMaxDevices) return -3;
+  if (g_static_scratch_addr[dev] == nullptr) {
+    // once per device, with that device current: resolve the symbol to a real device address
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_colsum_static_scratch);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    g_static_scratch_addr[dev] = ptr;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  unsigned int* counters = static_cast<unsigned int*>(g_static_scratch_addr[dev]);
+  float* part = reinterpret_cast<float*>(counters + kColreduceCounters);
+  // the previous call's leftovers must not be mistaken for arrivals of this one
+  e = cudaMemsetAsync(counters, 0, kColreduceCounters * sizeof(unsigned int), s);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  const int R = colreduce_splits(M, N);
+  dim3 grid((N + 255) / 256, R);
+  colreduce_kernel<0><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), nullptr, nullptr,
+                                           nullptr, part, counters, M, N, ld,
+                                           static_cast<__nv_bfloat16*>(out), nullptr, accumulate);
   return static_cast<int>(cudaGetLastError());
 }

@@ -66,6 +66,18 @@ int b200_layernorm_bwd_params(const void* dy, const void* x, const float* mean, 
 int b200_colsum(const void* dy, void* out, int M, int N, int ld, int accumulate, void* scratch,
                 size_t scratch_bytes, void* stream);
 
+/* Same result as b200_colsum, for callers that cannot allocate (no counterpart in the reference, which
+ * has no native entry points at all): a plug-in inside a framework whose pool already owns the GPU's
+ * memory, or a loop that must stay clear of cudaMalloc's driver locks and device synchronisation.
+ * The scratch is a 512 KiB device array built into the library (held by every GPU that loads it until
+ * exit), so no buffer is passed and nothing is allocated or freed.  The FIRST call on each device
+ * looks up the array's device address; make it before any stream capture.  All calls on a GPU share
+ * the one array: keep them stream-ordered, overlapping calls race.  Limit: N <= 65536 columns and
+ * scratch <= b200_colsum_static_max_bytes(); larger shapes return B200_ERR_STATIC_SCRATCH. */
+#define B200_ERR_STATIC_SCRATCH (-8)
+size_t b200_colsum_static_max_bytes(void);
+int b200_colsum_static(const void* dy, void* out, int M, int N, int ld, int accumulate, void* stream);
+
 /* ---- embedding (TH:85-89) ------------------------------------------------------ */
 int b200_embedding_fwd(const int* tokens, const void* wte, const void* wpe, void* out, int B,
                        int T, int d, float drop_p, unsigned int seed, void* stream);
