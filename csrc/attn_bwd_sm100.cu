@@ -37,8 +37,8 @@ constexpr int AB_HD = 64;
 constexpr int AB_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps), warpgroups 1-2: compute
 constexpr int AB_TILE = AB_BLK * AB_HD * 2;    // 16 KiB
 constexpr int AB_PBYTES = AB_BLK * AB_BLK * 2; // 32 KiB
-constexpr int AB_SMEM = 2 * AB_TILE /*K,V*/ + 4 * AB_TILE /*Q,dO x2*/ + 2 * AB_PBYTES /*P,dS*/ +
-                        3 * AB_BLK * 4 /*lse,D,keys*/ + 256 /*bars*/ + 1024 /*align*/;
+constexpr int AB_SMEM = 2 * AB_TILE /*K,V*/ + 4 * AB_TILE /*Q,dO x2*/ + 4 * AB_PBYTES /*P,dS x2*/ +
+                        3 * AB_BLK * 4 /*lse,D,keys*/ + 256 /*bars*/;   // 231168 B of the 232448 B limit
 
 struct AttnBwdParams {
   const float* lse;
@@ -63,16 +63,17 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 __global__ void __launch_bounds__(AB_THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
                 const __grid_constant__ CUtensorMap map_do, const AttnBwdParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // SWIZZLE_128B tiles need 1024-byte alignment; declaring the alignment (instead of rounding the
+  // pointer up through an integer) keeps the address space known, so accesses are LDS/STS.
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* sK = smem;
   uint8_t* sV = sK + AB_TILE;
   uint8_t* sQ = sV + AB_TILE;            // [2]
   uint8_t* sDO = sQ + 2 * AB_TILE;       // [2]
-  uint8_t* sP = sDO + 2 * AB_TILE;       // P^T  [128 keys][128 queries] bf16, two 64-query chunks
-  uint8_t* sDS = sP + AB_PBYTES;         // dS^T same layout
-  float* sLSE = reinterpret_cast<float*>(sDS + AB_PBYTES);  // [128] (already times log2e)
+  uint8_t* sP = sDO + 2 * AB_TILE;       // P^T  [2 buffers][128 keys][128 queries] bf16, two 64-query chunks each
+  uint8_t* sDS = sP + 2 * AB_PBYTES;     // dS^T same layout; buffer = query-block index & 1
+  float* sLSE = reinterpret_cast<float*>(sDS + 2 * AB_PBYTES);  // [128] (already times log2e)
   float* sD = sLSE + AB_BLK;                                 // [128]
   uint32_t* sKey = reinterpret_cast<uint32_t*>(sD + AB_BLK); // [128] dropout row keys
   uint64_t* bars = reinterpret_cast<uint64_t*>(sKey + AB_BLK);
@@ -140,12 +141,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       const uint32_t id_sdp = umma_idesc_bf16(AB_BLK, AB_BLK, false, false);
       const uint32_t id_dvk = umma_idesc_bf16(AB_BLK, AB_HD, false, true);
       const uint32_t id_dq = umma_idesc_bf16(AB_BLK, AB_HD, true, true);
-      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP), aDS = smem_u32(sDS);
+      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
       mbar_wait(kv_full, 0);
       tc_fence_after();
-      int st = 0;
+      int st = 0;               // Q/dO stage of the block whose S,dP are issued next
       uint32_t ph = 0, it_ph = 0;
-      for (int i = i_begin; i < nblk; ++i) {
+      auto issue_sdp = [&]() {  // S^T and dP^T of the next query block (its Q/dO are in stage st)
         mbar_wait(&qdo_full[st], ph);
         tc_fence_after();
         const uint32_t aQ = smem_u32(sQ + st * AB_TILE), aDO = smem_u32(sDO + st * AB_TILE);
@@ -158,9 +159,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
           umma_bf16_ss(tmem_base + TC_DP, umma_smem_desc(aV + k * 32, 16, 1024),
                        umma_smem_desc(aDO + k * 32, 16, 1024), id_sdp, k ? 1u : 0u);
         umma_commit(sdp_full);
-        mbar_wait(pds_full, it_ph);        // P^T and dS^T are in shared memory
-        mbar_wait(dq_empty, it_ph ^ 1);    // previous dQ tile has been drained
+        if (++st == 2) { st = 0; ph ^= 1; }
+      };
+      if (i_begin < nblk) issue_sdp();
+      for (int i = i_begin; i < nblk; ++i) {
+        const int buf = (i - i_begin) & 1;      // P/dS buffer and Q/dO stage of block i
+        mbar_wait(pds_full, it_ph);             // P^T(i), dS^T(i) are in shared memory; S/dP TMEM is free
         tc_fence_after();
+        if (i + 1 < nblk) issue_sdp();          // next block's scores first: the compute warps start on
+                                                // them while the three products below run
+        mbar_wait(dq_empty, it_ph ^ 1);         // previous dQ tile has been drained
+        tc_fence_after();
+        const uint32_t aQ = smem_u32(sQ + buf * AB_TILE), aDO = smem_u32(sDO + buf * AB_TILE);
+        const uint32_t aP = smem_u32(sP + buf * AB_PBYTES), aDS = smem_u32(sDS + buf * AB_PBYTES);
         const uint32_t acc = (i > i_begin) ? 1u : 0u;
 #pragma unroll
         for (int k = 0; k < AB_BLK / 16; ++k) {
@@ -178,10 +189,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
         for (int k = 0; k < AB_BLK / 16; ++k)
           umma_bf16_ss(tmem_base + TC_DQ, umma_smem_desc(aDS + k * 2048, AB_BLK * 128, 1024),
                        umma_smem_desc(aK + k * 2048, AB_BLK * 128, 1024), id_dq, k ? 1u : 0u);
-        umma_commit(&qdo_empty[st]);
+        umma_commit(&qdo_empty[buf]);
         umma_commit(dq_full);
         it_ph ^= 1;
-        if (++st == 2) { st = 0; ph ^= 1; }
       }
     }
   }
@@ -199,8 +209,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     const uint32_t thr16 = p.drop_threshold;
     const uint32_t kpair = static_cast<uint32_t>(krow >> 1);
     const uint32_t kshift = (krow & 1) ? 0u : 16u;
-    uint8_t* rowP = sP + wg * (AB_BLK * 128) + r * 128;
-    uint8_t* rowS = sDS + wg * (AB_BLK * 128) + r * 128;
+    uint8_t* rowP = nullptr;   // set per query block: P/dS buffer (i & 1)
+    uint8_t* rowS = nullptr;
     uint32_t it_ph = 0;
 
     // One (key block, query block) tile for this thread's key row and its 64 query columns.
@@ -275,8 +285,30 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       }
     };
 
+    // dQ of query block qi: rows = queries, this thread adds 32 of the 64 head-dim columns
+    auto drain_dq = [&](int qi, uint32_t phase) {
+      mbar_wait(dq_full, phase);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DQ + wg * 32, v);
+      tmem_ld_wait();
+      const int q = qi * AB_BLK + r;
+      if (q < p.T) {
+        float* dst = p.dq_acc + static_cast<size_t>(row_base + q) * p.d + h * AB_HD + wg * 32;
+#pragma unroll
+        for (int e = 0; e < 32; e += 4)
+          red_add_v4(dst + e, __uint_as_float(v[e]) * p.scale, __uint_as_float(v[e + 1]) * p.scale,
+                     __uint_as_float(v[e + 2]) * p.scale, __uint_as_float(v[e + 3]) * p.scale);
+      }
+      tc_fence_before();
+      mbar_arrive(dq_empty);
+    };
+
     for (int i = i_begin; i < nblk; ++i) {
       const int q0 = i * AB_BLK;
+      const int buf = (i - i_begin) & 1;
+      rowP = sP + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
+      rowS = sDS + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
       // stage LSE (times log2e), D and the dropout row keys for the 128 queries of this block
       if (tid < AB_BLK) {
         const int q = q0 + tid;
@@ -289,33 +321,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(sdp_full, it_ph);
       tc_fence_after();
+      // buffer (i & 1) was last read by the products of block i-2, whose completion (dq_full) every
+      // thread observed when it drained dQ(i-2) during the previous iteration
       const bool edge = (k0 + AB_BLK > p.T) || (q0 + AB_BLK > p.T) || (p.causal && i == jb);
       if (edge) tile_body(std::true_type{}, q0); else tile_body(std::false_type{}, q0);
+      asm volatile("bar.sync 1, 256;" ::: "memory");   // everyone is done with sLSE / sD / sKey
       tc_fence_before();
       fence_proxy_async();
       mbar_arrive(pds_full);
-      // ---- drain dQ_i: rows = queries, this thread takes 32 of the 64 head-dim columns ----
-      mbar_wait(dq_full, it_ph);
-      tc_fence_after();
-      {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DQ + wg * 32, v);
-        tmem_ld_wait();
-        const int q = q0 + r;
-        if (q < p.T) {
-          float* dst = p.dq_acc + static_cast<size_t>(row_base + q) * p.d + h * AB_HD + wg * 32;
-#pragma unroll
-          for (int e = 0; e < 32; e += 4)
-            red_add_v4(dst + e, __uint_as_float(v[e]) * p.scale, __uint_as_float(v[e + 1]) * p.scale,
-                       __uint_as_float(v[e + 2]) * p.scale, __uint_as_float(v[e + 3]) * p.scale);
-        }
-      }
-      tc_fence_before();
-      mbar_arrive(dq_empty);
+      // the previous block's dQ is (about to be) complete: drain it while S,dP of the next block and the
+      // dV/dK/dQ products of this one run on the tensor cores
+      if (i > i_begin) drain_dq(i - 1, it_ph ^ 1);
       it_ph ^= 1;
     }
+    if (i_begin < nblk) drain_dq(nblk - 1, it_ph ^ 1);
     // ---- epilogue: dV (warpgroup 0) and dK (warpgroup 1), rows = keys ------------------------
-    // The last dq_full wait above also covers the final dV / dK MMAs (same commit).
+    // The last dq_full wait (final drain above) also covers the final dV / dK MMAs (same commit).
     if (i_begin < nblk) {
       const uint32_t tcol = (wg == 0) ? TC_DV : TC_DK;
       const float oscale = (wg == 0) ? 1.f : p.scale;   // softmax scale folded out of dS

@@ -57,9 +57,10 @@ struct AttnFwdParams {
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // SWIZZLE_128B tiles need 1024-byte alignment; declaring the alignment (instead of rounding the
+  // pointer up through an integer) keeps the address space known, so accesses are LDS/STS.
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + AT_TILE;
   uint8_t* sV = sK + AT_KV_STAGES * AT_TILE;

@@ -23,6 +23,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <type_traits>
+
 #include "b200_internal.h"
 #include "sm100_ptx.cuh"
 
@@ -61,8 +63,8 @@ struct GemmCfg {
   static constexpr int kBBytes = BN * GEMM_BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN;  // 256 or 512, power of two
-  static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + align slack
+  static constexpr int kBarBytes = 256 + 2 * BN * 4;   // barriers + double-buffered fp32 bias slice
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes;
 };
 
 struct GemmParams {
@@ -106,10 +108,10 @@ __global__ void __launch_bounds__(GEMM_THREADS + GEMM_GATHER_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                          const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  // SWIZZLE_128B tiles need 1024-byte alignment.
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // SWIZZLE_128B tiles need 1024-byte alignment; declaring the alignment (instead of rounding the
+  // pointer up through an integer) keeps the address space known, so accesses are LDS/STS.
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* tiles = smem;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
   uint64_t* full_bar = bars;                         // [kStages]
@@ -289,105 +291,125 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   } else if (warp < 6) {
     // ================================ epilogue ====================================
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const int et = threadIdx.x - 64;   // 0..127 among the epilogue threads
     const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
+    float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);   // [2][BN] floats, double-buffered per tile
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
-      const int n0 = (tile / p.num_m_tiles) * BN;
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
+    int tile_no = 0;
+
+    // One output tile.  EPI is a compile-time constant inside, so each epilogue kind gets a tight loop:
+    // aux (residual / pre-activation / old D) for chunk c+1 is requested before chunk c is processed,
+    // the bias comes from shared memory, TMEM is read 32 columns at a time.
+    auto run_tile = [&](auto epi_c, int m0, int n0, const float* bias_s) {
+      constexpr int EPI = decltype(epi_c)::value;
+      constexpr bool HAS_BIAS = (EPI == B200_EPI_BIAS || EPI == B200_EPI_BIAS_GELU || EPI == B200_EPI_BIAS_RESID);
+      constexpr bool HAS_AUX = (EPI == B200_EPI_BIAS_RESID || EPI == B200_EPI_DGELU || EPI == B200_EPI_ACCUM);
       const int row = m0 + quarter * 32 + lane;
       const bool row_ok = row < p.M;
-      const size_t row_off = static_cast<size_t>(row) * p.ldd;
+      const size_t row_off = static_cast<size_t>(row_ok ? row : 0) * p.ldd;
+      const __nv_bfloat16* auxp = (EPI == B200_EPI_ACCUM) ? p.D : p.aux;
       const uint32_t taddr_row =
           tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      uint4 aux_cur[4], aux_nxt[4];
+      auto load_aux = [&](int c, uint4 (&dst)[4]) {
+        if (HAS_AUX) {
+          const int col0 = n0 + c * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            if (row_ok && col0 + g * 8 < p.N)
+              dst[g] = *reinterpret_cast<const uint4*>(auxp + row_off + col0 + g * 8);
+        }
+      };
+      load_aux(0, aux_cur);
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr_row + c * 32, r);
+        if (c + 1 < BN / 32) load_aux(c + 1, aux_nxt);
         tmem_ld_wait();
         const int col0 = n0 + c * 32;
         if (row_ok && col0 < p.N) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {  // 8 columns (16 B of bf16) per group
             const int col = col0 + g * 8;
-            if (col >= p.N) break;
-            float v[8];
+            if (col < p.N) {
+              float v[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-            if (p.epi == B200_EPI_BIAS || p.epi == B200_EPI_BIAS_GELU ||
-                p.epi == B200_EPI_BIAS_RESID) {
-              const uint4 bv = __ldg(reinterpret_cast<const uint4*>(p.bias + col));
-              const uint32_t bw[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(bw[j]);
-                v[2 * j] += f.x;
-                v[2 * j + 1] += f.y;
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+              if (HAS_BIAS) {
+                const float4 b0 = *reinterpret_cast<const float4*>(bias_s + c * 32 + g * 8);
+                const float4 b1 = *reinterpret_cast<const float4*>(bias_s + c * 32 + g * 8 + 4);
+                v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+                v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
               }
-            }
-            if (p.epi == B200_EPI_BIAS_GELU) {
-              // pre-activation -> D, activation -> D2
-              uint4 o;
-              o.x = pack_bf16x2(v[0], v[1]);
-              o.y = pack_bf16x2(v[2], v[3]);
-              o.z = pack_bf16x2(v[4], v[5]);
-              o.w = pack_bf16x2(v[6], v[7]);
-              *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
+              if (EPI == B200_EPI_BIAS_GELU) {   // pre-activation -> D, activation -> D2
+                uint4 o;
+                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
-              o.x = pack_bf16x2(v[0], v[1]);
-              o.y = pack_bf16x2(v[2], v[3]);
-              o.z = pack_bf16x2(v[4], v[5]);
-              o.w = pack_bf16x2(v[6], v[7]);
-              *reinterpret_cast<uint4*>(p.D2 + row_off + col) = o;
-              continue;
-            }
-            if (p.epi == B200_EPI_BIAS_RESID) {
-              if (p.drop_threshold) {
+                for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
+                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(p.D2 + row_off + col) = o;
+              } else {
+                if (EPI == B200_EPI_BIAS_RESID && p.drop_threshold) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  const uint64_t idx = static_cast<uint64_t>(row) * p.N + (col + j);
-                  v[j] = dropout_keep(seed, idx, p.drop_threshold) ? v[j] * p.drop_scale
-                                                                          : 0.0f;
+                  for (int j = 0; j < 8; ++j) {
+                    const uint64_t idx = static_cast<uint64_t>(row) * p.N + (col + j);
+                    v[j] = dropout_keep(seed, idx, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
+                  }
                 }
-              }
-              const uint4 xv = *reinterpret_cast<const uint4*>(p.aux + row_off + col);
-              const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+                if (HAS_AUX) {
+                  const uint32_t xw[4] = {aux_cur[g].x, aux_cur[g].y, aux_cur[g].z, aux_cur[g].w};
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(xw[j]);
-                v[2 * j] += f.x;
-                v[2 * j + 1] += f.y;
-              }
-            } else if (p.epi == B200_EPI_DGELU) {
-              const uint4 xv = *reinterpret_cast<const uint4*>(p.aux + row_off + col);
-              const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(xw[j]);
-                v[2 * j] *= gelu_erf_grad(f.x);
-                v[2 * j + 1] *= gelu_erf_grad(f.y);
-              }
-            } else if (p.epi == B200_EPI_ACCUM) {
-              const uint4 xv = *reinterpret_cast<const uint4*>(p.D + row_off + col);
-              const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 f = unpack_bf16x2(xw[j]);
-                v[2 * j] += f.x;
-                v[2 * j + 1] += f.y;
+                  for (int j = 0; j < 4; ++j) {
+                    const float2 f = unpack_bf16x2(xw[j]);
+                    if (EPI == B200_EPI_DGELU) {
+                      v[2 * j] *= gelu_erf_grad(f.x);
+                      v[2 * j + 1] *= gelu_erf_grad(f.y);
+                    } else {   // residual add / accumulate
+                      v[2 * j] += f.x;
+                      v[2 * j + 1] += f.y;
+                    }
+                  }
+                }
+                uint4 o;
+                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
               }
             }
-            uint4 o;
-            o.x = pack_bf16x2(v[0], v[1]);
-            o.y = pack_bf16x2(v[2], v[3]);
-            o.z = pack_bf16x2(v[4], v[5]);
-            o.w = pack_bf16x2(v[6], v[7]);
-            *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
           }
         }
+        if (HAS_AUX) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) aux_cur[g] = aux_nxt[g];
+        }
+      }
+    };
+
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
+      const int n0 = (tile / p.num_m_tiles) * BN;
+      float* bias_s = s_bias + (tile_no & 1) * BN;
+      ++tile_no;
+      if (p.epi == B200_EPI_BIAS || p.epi == B200_EPI_BIAS_GELU || p.epi == B200_EPI_BIAS_RESID) {
+        // stage this tile's bias slice once (overlaps the main loop still running for this tile)
+        for (int i = et; i < BN; i += 128)
+          bias_s[i] = (n0 + i < p.N) ? __bfloat162float(p.bias[n0 + i]) : 0.f;
+        asm volatile("bar.sync 3, 128;" ::: "memory");
+      }
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      switch (p.epi) {
+        case B200_EPI_BIAS: run_tile(std::integral_constant<int, B200_EPI_BIAS>{}, m0, n0, bias_s); break;
+        case B200_EPI_BIAS_GELU: run_tile(std::integral_constant<int, B200_EPI_BIAS_GELU>{}, m0, n0, bias_s); break;
+        case B200_EPI_BIAS_RESID: run_tile(std::integral_constant<int, B200_EPI_BIAS_RESID>{}, m0, n0, bias_s); break;
+        case B200_EPI_DGELU: run_tile(std::integral_constant<int, B200_EPI_DGELU>{}, m0, n0, bias_s); break;
+        case B200_EPI_ACCUM: run_tile(std::integral_constant<int, B200_EPI_ACCUM>{}, m0, n0, bias_s); break;
+        default: run_tile(std::integral_constant<int, B200_EPI_NONE>{}, m0, n0, bias_s); break;
       }
       // all tcgen05.ld of this warp are complete (wait::ld above): release the accumulator
       tc_fence_before();
