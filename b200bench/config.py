@@ -16,7 +16,10 @@ from typing import Any, Dict, Optional
 TIERS: Dict[str, Dict[str, int]] = {
     "A": dict(vocab_size=32000, n_embd=1024, n_head=16, n_layer=16),
     "B": dict(vocab_size=32000, n_embd=2048, n_head=32, n_layer=32),
-    "7B": dict(vocab_size=32000, n_embd=4096, n_head=32, n_layer=32),
+    # 7B-shaped decoder (6.58 B params: L=32, d=4096, V=32000).  The reference sketches it with 32 heads of
+    # 128 (docs/ARCHITECTURE.md:452-461); the native attention kernels are built for head_dim 64, so the
+    # native tier uses 64 heads of 64 — same parameter count, same GEMM shapes, same attention FLOPs.
+    "7B": dict(vocab_size=32000, n_embd=4096, n_head=64, n_layer=32),
     "T": dict(vocab_size=512, n_embd=128, n_head=2, n_layer=2),
 }
 

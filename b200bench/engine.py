@@ -460,6 +460,27 @@ class NativeEngine:
         self._launches_per_step = eager + (self._graph_launches if self._graphs else 0)
         return self.loss
 
+    def profile_breakdown(self) -> Dict[str, float]:
+        """Per-phase device times (ms) of one optimizer step, run eagerly with CUDA events between the
+        phases (the reference has no profiling hooks).  Call between training steps, on an
+        accumulation boundary.  The step is a real one: weights are updated."""
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        if self.dropout > 0:
+            self.ops.step_seed_advance()
+        self._gseq = 0
+        ev[0].record()
+        self._forward()
+        ev[1].record()
+        self._loss_and_backward(True, True)      # includes the overlapped DDP all-reduces and their join
+        ev[2].record()
+        self.micro = 0
+        self._optimizer_boundary()
+        ev[3].record()
+        torch.cuda.synchronize(self.device)
+        out = {"forward_ms": ev[0].elapsed_time(ev[1]), "backward_ms": ev[1].elapsed_time(ev[2]),
+               "optimizer_and_comm_ms": ev[2].elapsed_time(ev[3]), "total_ms": ev[0].elapsed_time(ev[3])}
+        return {k: round(v, 3) for k, v in out.items()}
+
     # ---------------------------------------------------------------------------------------
     def _full_params(self) -> torch.Tensor:
         if not self.sharded_params:

@@ -33,7 +33,7 @@ namespace b200 {
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
 constexpr int GEMM_THREADS = 192;
-constexpr int GEMM_GATHER_THREADS = 128;   // 4 extra warps in gather mode
+constexpr int GEMM_GATHER_THREADS = 64;    // 2 extra warps in gather mode (256 threads total: no register cap below 255)
 
 __device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* addr) {
   uint32_t v;
@@ -56,15 +56,18 @@ __device__ __forceinline__ void fence_proxy_async_global() {
   asm volatile("fence.proxy.async.global;" ::: "memory");
 }
 
-template <int BN>
+template <int BN, int CTAS>
 struct GemmCfg {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kBNLocal = BN / CTAS;             // B rows held by each CTA of the pair
   static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;  // 16 KiB
-  static constexpr int kBBytes = BN * GEMM_BK * 2;
+  static constexpr int kBBytes = kBNLocal * GEMM_BK * 2;
+  static constexpr int kStagingBytes = 32768;            // TMA-store staging of the epilogue
+  static constexpr int kBarBytes = 256 + 2 * BN * 4;     // barriers + double-buffered fp32 bias slice
+  static constexpr int kRing = 232448 - kStagingBytes - kBarBytes;   // what is left of the 227 KiB
+  static constexpr int kStages = (kRing / (kABytes + kBBytes)) > 8 ? 8 : (kRing / (kABytes + kBBytes));
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN;  // 256 or 512, power of two
-  static constexpr int kBarBytes = 256 + 2 * BN * 4;   // barriers + double-buffered fp32 bias slice
-  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBarBytes;
 };
 
 struct GemmParams {
@@ -103,17 +106,30 @@ struct GemmParams {
   uint32_t* pf_flags;
 };
 
-template <int BN>
+// CTAS = 1: one CTA per 128 x BN tile (cta_group::1).
+// CTAS = 2: a CTA pair (2-CTA cluster) per 256 x BN tile (cta_group::2): each CTA stages its own 128 rows
+//           of A and HALF of B, the leader issues M=256 MMAs that read both halves, so the shared-memory
+//           traffic per MAC halves for B — at 128x128 per CTA the single-CTA kernel is shared-memory-bound
+//           (operand reads + TMA fills = 2 x 128 B/clk), which caps it near 50 % of the tensor peak.
+template <int BN, int CTAS>
 __global__ void __launch_bounds__(GEMM_THREADS + GEMM_GATHER_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
-                         const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+                         const __grid_constant__ CUtensorMap map_b,
+                         const __grid_constant__ CUtensorMap map_d,
+                         const __grid_constant__ CUtensorMap map_d2, const GemmParams p) {
+  using Cfg = GemmCfg<BN, CTAS>;
+  constexpr int BNL = Cfg::kBNLocal;
+  const uint32_t cta_rank = (CTAS == 2) ? cluster_ctarank() : 0u;
+  const bool is_leader = cta_rank == 0;
+  const int unit = blockIdx.x / CTAS;          // tile-scheduling unit: a CTA or a CTA pair
+  const int num_units = gridDim.x / CTAS;
   // SWIZZLE_128B tiles need 1024-byte alignment; declaring the alignment (instead of rounding the
   // pointer up through an integer) keeps the address space known, so accesses are LDS/STS.
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* tiles = smem;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint8_t* stg = smem + Cfg::kStages * Cfg::kStageBytes;   // epilogue staging: 4 warps x 2 x 4 KiB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + Cfg::kStagingBytes);
   uint64_t* full_bar = bars;                         // [kStages]
   uint64_t* empty_bar = bars + Cfg::kStages;         // [kStages]
   uint64_t* tfull_bar = bars + 2 * Cfg::kStages;     // [2]
@@ -128,21 +144,23 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_d);
     for (int s = 0; s < Cfg::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);  // one arrive per epilogue warp
+      mbar_init(&tempty_bar[s], 4 * CTAS);  // one arrive per epilogue warp (of both CTAs of a pair)
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    if (CTAS == 2) tmem_alloc_2cta(tmem_slot, Cfg::kTmemCols); else tmem_alloc(tmem_slot, Cfg::kTmemCols);
   }
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();   // the peer's barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -162,11 +180,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           if (++spins > (1u << 28)) __trap();
         }
       };
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
-        const int n0 = (tile / p.num_m_tiles) * BN;
-        if (gather && !p.b_mn) {   // B rows = n: this tile needs the chunks covering [n0, n0+BN)
-          const int n1 = (n0 + BN < p.g_rows ? n0 + BN : p.g_rows) - 1;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        const int m0 = (tile % p.num_m_tiles) * (GEMM_BM * CTAS) + static_cast<int>(cta_rank) * GEMM_BM;
+        const int n0 = (tile / p.num_m_tiles) * BN + static_cast<int>(cta_rank) * BNL;   // this CTA's B rows
+        if (gather && !p.b_mn) {   // B rows = n: this CTA needs the chunks covering [n0, n0+BNL)
+          const int n1 = (n0 + BNL < p.g_rows ? n0 + BNL : p.g_rows) - 1;
           for (int c = n0 / p.g_chunk_rows; c <= n1 / p.g_chunk_rows; ++c) wait_chunk(c);
           fence_proxy_async_global();
         }
@@ -180,21 +198,24 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = tiles + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          // pair mode: all bytes (of both CTAs) are credited to the leader's barrier; only it arrives
+          if (is_leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           const int k0 = kb * GEMM_BK;
+          auto load = [&](const CUtensorMap* m, void* dst, int c0, int c1) {
+            if (CTAS == 2) tma_load_2d_2cta(m, &full_bar[stage], dst, c0, c1);
+            else tma_load_2d(m, &full_bar[stage], dst, c0, c1);
+          };
           if (!p.a_mn) {
-            tma_load_2d(&map_a, &full_bar[stage], sa, k0, m0);
+            load(&map_a, sa, k0, m0);
           } else {
 #pragma unroll
-            for (int c = 0; c < GEMM_BM / 64; ++c)
-              tma_load_2d(&map_a, &full_bar[stage], sa + c * (GEMM_BK * 128), m0 + 64 * c, k0);
+            for (int c = 0; c < GEMM_BM / 64; ++c) load(&map_a, sa + c * (GEMM_BK * 128), m0 + 64 * c, k0);
           }
           if (!p.b_mn) {
-            tma_load_2d(&map_b, &full_bar[stage], sb, k0, n0);
+            load(&map_b, sb, k0, n0);
           } else {
 #pragma unroll
-            for (int c = 0; c < BN / 64; ++c)
-              tma_load_2d(&map_b, &full_bar[stage], sb + c * (GEMM_BK * 128), n0 + 64 * c, k0);
+            for (int c = 0; c < BNL / 64; ++c) load(&map_b, sb + c * (GEMM_BK * 128), n0 + 64 * c, k0);
           }
           if (++stage == Cfg::kStages) {
             stage = 0;
@@ -207,7 +228,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   } else if (warp >= 6) {
     // ================================ K14 gather warps =============================
     if (p.gather_ws > 0) {
-      const int gt = threadIdx.x - GEMM_THREADS;   // 0..127
+      const int gt = threadIdx.x - GEMM_THREADS;   // 0..63
       const uint32_t E = *p.g_epoch;
       auto gather_job = [&](unsigned long long flat_off, int rows, int cols, __nv_bfloat16* out,
                             uint32_t* flags, uint32_t publish) {
@@ -239,7 +260,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           }
           __threadfence();
           fence_proxy_async_global();
-          asm volatile("bar.sync 2, 128;" ::: "memory");
+          asm volatile("bar.sync 2, 64;" ::: "memory");
           if (gt == 0) st_release_gpu_u32(flags + c, publish);
         }
       };
@@ -248,8 +269,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, p.a_mn != 0, p.b_mn != 0);
+    if (lane == 0 && is_leader) {
+      const uint32_t idesc = umma_idesc_bf16(GEMM_BM * CTAS, BN, p.a_mn != 0, p.b_mn != 0);
       // K-major: +32 B per 16-element K step inside the 128 B swizzle row.
       // MN-major: +16 k-rows * 128 B = 2048 B per K step; MN chunks are BK*128 B apart.
       const uint32_t a_kstep = p.a_mn ? 2048u : 32u;
@@ -260,7 +281,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -273,15 +294,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           for (int k = 0; k < GEMM_BK / 16; ++k) {
             const uint64_t adesc = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
             const uint64_t bdesc = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
-            umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+            if (CTAS == 2) umma_bf16_ss_2cta(tmem_d, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+            else umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          // smem slot reusable (in both CTAs of a pair) once these MMAs retire
+          if (CTAS == 2) umma_commit_2cta(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
           if (++stage == Cfg::kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs)
+        if (CTAS == 2) umma_commit_2cta(&tfull_bar[acc]); else umma_commit(&tfull_bar[acc]);
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -300,11 +324,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
 
     // One output tile.  EPI is a compile-time constant inside, so each epilogue kind gets a tight loop:
     // aux (residual / pre-activation / old D) for chunk c+1 is requested before chunk c is processed,
-    // the bias comes from shared memory, TMEM is read 32 columns at a time.
+    // the bias comes from shared memory, TMEM is read 32 columns at a time.  Results do not go to global
+    // memory from the registers (that would be 32 half-filled sectors per warp store): each warp packs
+    // its 32 rows x 64 columns into a 128B-swizzled 4 KiB staging tile and one lane hands it to the TMA
+    // store engine, which also clips rows >= M and columns >= N.
+    uint8_t* stg_w = stg + quarter * 8192;    // this warp's two 4 KiB staging tiles
+    uint32_t nst = 0;
     auto run_tile = [&](auto epi_c, int m0, int n0, const float* bias_s) {
       constexpr int EPI = decltype(epi_c)::value;
       constexpr bool HAS_BIAS = (EPI == B200_EPI_BIAS || EPI == B200_EPI_BIAS_GELU || EPI == B200_EPI_BIAS_RESID);
       constexpr bool HAS_AUX = (EPI == B200_EPI_BIAS_RESID || EPI == B200_EPI_DGELU || EPI == B200_EPI_ACCUM);
+      constexpr bool DUAL = (EPI == B200_EPI_BIAS_GELU);
       const int row = m0 + quarter * 32 + lane;
       const bool row_ok = row < p.M;
       const size_t row_off = static_cast<size_t>(row_ok ? row : 0) * p.ldd;
@@ -322,63 +352,92 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         }
       };
       load_aux(0, aux_cur);
+      uint8_t* buf0 = nullptr;
+      uint8_t* buf1 = nullptr;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr_row + c * 32, r);
         if (c + 1 < BN / 32) load_aux(c + 1, aux_nxt);
+        if ((c & 1) == 0) {
+          // claim staging for this 64-column chunk: a tile is free once the store issued from it has
+          // finished READING shared memory
+          if (DUAL) {
+            if (lane == 0) tma_store_wait_read<0>();
+            buf0 = stg_w;
+            buf1 = stg_w + 4096;
+          } else {
+            if (lane == 0) tma_store_wait_read<1>();
+            buf0 = stg_w + (nst & 1) * 4096;
+            ++nst;
+          }
+          __syncwarp();
+        }
         tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (row_ok && col0 < p.N) {
+        uint8_t* row0 = buf0 + lane * 128;
+        uint8_t* row1 = DUAL ? buf1 + lane * 128 : nullptr;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {  // 8 columns (16 B of bf16) per group
-            const int col = col0 + g * 8;
-            if (col < p.N) {
-              float v[8];
+        for (int g = 0; g < 4; ++g) {  // 8 columns (16 B of bf16) per group
+          const int sw = ((((c & 1) * 4 + g) ^ (lane & 7)) << 4);   // 128B-swizzled 16-byte slot
+          uint4 o;
+          const int col = n0 + c * 32 + g * 8;
+          float v[8];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-              if (HAS_BIAS) {
-                const float4 b0 = *reinterpret_cast<const float4*>(bias_s + c * 32 + g * 8);
-                const float4 b1 = *reinterpret_cast<const float4*>(bias_s + c * 32 + g * 8 + 4);
-                v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-                v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+          if (HAS_BIAS) {
+            const float4 b0 = *reinterpret_cast<const float4*>(bias_s + c * 32 + g * 8);
+            const float4 b1 = *reinterpret_cast<const float4*>(bias_s + c * 32 + g * 8 + 4);
+            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+          }
+          if (DUAL) {   // pre-activation -> D, activation -> D2
+            o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(row0 + sw) = o;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
+            o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(row1 + sw) = o;
+          } else {
+            if (EPI == B200_EPI_BIAS_RESID && p.drop_threshold) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const uint64_t idx = static_cast<uint64_t>(row) * p.N + (col + j);
+                v[j] = dropout_keep(seed, idx, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
               }
-              if (EPI == B200_EPI_BIAS_GELU) {   // pre-activation -> D, activation -> D2
-                uint4 o;
-                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
-                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
-                *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
+            }
+            if (HAS_AUX) {
+              const bool ok = row_ok && col < p.N;     // out-of-range aux was never loaded
+              const uint32_t xw[4] = {aux_cur[g].x, aux_cur[g].y, aux_cur[g].z, aux_cur[g].w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
-                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
-                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
-                *reinterpret_cast<uint4*>(p.D2 + row_off + col) = o;
-              } else {
-                if (EPI == B200_EPI_BIAS_RESID && p.drop_threshold) {
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    const uint64_t idx = static_cast<uint64_t>(row) * p.N + (col + j);
-                    v[j] = dropout_keep(seed, idx, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
-                  }
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = ok ? unpack_bf16x2(xw[j]) : make_float2(0.f, 0.f);
+                if (EPI == B200_EPI_DGELU) {
+                  v[2 * j] *= gelu_erf_grad(f.x);
+                  v[2 * j + 1] *= gelu_erf_grad(f.y);
+                } else {   // residual add / accumulate
+                  v[2 * j] += f.x;
+                  v[2 * j + 1] += f.y;
                 }
-                if (HAS_AUX) {
-                  const uint32_t xw[4] = {aux_cur[g].x, aux_cur[g].y, aux_cur[g].z, aux_cur[g].w};
-#pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    const float2 f = unpack_bf16x2(xw[j]);
-                    if (EPI == B200_EPI_DGELU) {
-                      v[2 * j] *= gelu_erf_grad(f.x);
-                      v[2 * j + 1] *= gelu_erf_grad(f.y);
-                    } else {   // residual add / accumulate
-                      v[2 * j] += f.x;
-                      v[2 * j + 1] += f.y;
-                    }
-                  }
-                }
-                uint4 o;
-                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
-                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
-                *reinterpret_cast<uint4*>(p.D + row_off + col) = o;
+              }
+            }
+            o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(row0 + sw) = o;
+          }
+        }
+        if (c & 1) {
+          fence_proxy_async();     // generic-proxy smem writes -> visible to the TMA engine
+          __syncwarp();
+          if (lane == 0) {
+            const int col64 = n0 + (c >> 1) * 64;
+            if (col64 < p.N) {
+              tma_store_2d(&map_d, buf0, col64, m0 + quarter * 32);
+              tma_store_commit();
+              if (DUAL) {
+                tma_store_2d(&map_d2, buf1, col64, m0 + quarter * 32);
+                tma_store_commit();
               }
             }
           }
@@ -390,8 +449,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       }
     };
 
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile % p.num_m_tiles) * GEMM_BM;
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      const int m0 = (tile % p.num_m_tiles) * (GEMM_BM * CTAS) + static_cast<int>(cta_rank) * GEMM_BM;
       const int n0 = (tile / p.num_m_tiles) * BN;
       float* bias_s = s_bias + (tile_no & 1) * BN;
       ++tile_no;
@@ -414,19 +473,23 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       // all tcgen05.ld of this warp are complete (wait::ld above): release the accumulator
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (CTAS == 2) mbar_arrive_leader(&tempty_bar[acc]); else mbar_arrive(&tempty_bar[acc]);
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
     }
+    if (lane == 0) tma_store_wait<0>();   // staging must stay valid until the last store has drained
   }
 
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();   // neither CTA leaves (or frees TMEM) while the pair may still touch it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    if (CTAS == 2) tmem_dealloc_2cta(tmem_base, Cfg::kTmemCols); else tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
@@ -478,29 +541,42 @@ int device_sm_count() {
   return sms[dev];
 }
 
-template <int BN>
-static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams& p, int max_ctas,
-                       cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
-  static bool attr_done[64] = {false};
+template <int BN, int CTAS>
+static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md,
+                       const CUtensorMap& md2, GemmParams& p, int max_ctas, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN, CTAS>;
+  static bool attr_done[64] = {false};   // one flag set per template instantiation
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_done[dev & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>,
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, CTAS>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done[dev & 63] = true;
   }
-  p.num_m_tiles = (p.M + GEMM_BM - 1) / GEMM_BM;
+  p.num_m_tiles = (p.M + GEMM_BM * CTAS - 1) / (GEMM_BM * CTAS);
   p.num_n_tiles = (p.N + BN - 1) / BN;
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   int grid = device_sm_count();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (tiles < grid) grid = tiles;
+  if (tiles * CTAS < grid) grid = tiles * CTAS;
+  grid -= grid % CTAS;
+  if (grid < CTAS) grid = CTAS;
   const int threads = GEMM_THREADS + (p.gather_ws > 0 ? GEMM_GATHER_THREADS : 0);
-  gemm_bf16_tcgen05_kernel<BN><<<grid, threads, Cfg::kSmemBytes, stream>>>(ma, mb, p);
-  return static_cast<int>(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<BN, CTAS>, ma, mb, md, md2, p));
 }
 
 }  // namespace b200
@@ -530,16 +606,31 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if ((N % 8) || (K % 8) || (lda % 8) || (ldb % 8) || (ldd % 8)) return -2;
   if (a_mn && (M % 8)) return -2;
-  int BN = bn_hint;
+  // bn_hint: 0 = auto, 128 / 256 = single-CTA tile width, 2128 / 2256 = CTA-pair (cta_group::2) mode
+  int BN = bn_hint % 1000, CTAS = bn_hint >= 2000 ? 2 : 1;
   if (BN != 128 && BN != 256) {
-    // Pick the tile width that wastes the fewest SM-waves.
+    // Pick (pair mode, tile width) by a wave model: rounds of tiles over the scheduling units times the
+    // per-tile main-loop time, with the shared-memory-bandwidth efficiency of each shape
+    // (128x128: operand reads + TMA fills = 2 x 128 B/clk -> ~0.5; 128x256 and pair 256x128: ~0.68;
+    //  pair 256x256: ~0.95 — see profiles/README.md).
     const int sms = device_sm_count();
-    const int mt = (M + GEMM_BM - 1) / GEMM_BM;
-    const long t128 = static_cast<long>(mt) * ((N + 127) / 128);
-    const long t256 = static_cast<long>(mt) * ((N + 255) / 256);
-    const long w128 = (t128 + sms - 1) / sms;       // cost units: 1 per wave
-    const long w256 = 2 * ((t256 + sms - 1) / sms);  // a 256-wide tile costs two units
-    BN = (w256 <= w128 && N >= 256) ? 256 : 128;
+    struct Cand { int bn, ctas; double eff; };
+    const Cand cands[4] = {{128, 1, 0.50}, {256, 1, 0.68}, {128, 2, 0.68}, {256, 2, 0.95}};
+    double best = 1e30;
+    for (const Cand& c : cands) {
+      if (c.bn > 128 && N < 256) continue;
+      if (c.ctas == 2 && M <= 128) continue;
+      const long mt = (M + 128 * c.ctas - 1) / (128 * c.ctas);
+      const long nt = (N + c.bn - 1) / c.bn;
+      const long units = sms / c.ctas;
+      const long rounds = (mt * nt + units - 1) / units;
+      const double cost = rounds * (c.bn / 128.0) / c.eff + 0.15 * rounds;   // + per-tile epilogue/issue overhead
+      if (cost < best - 1e-9) {
+        best = cost;
+        BN = c.bn;
+        CTAS = c.ctas;
+      }
+    }
   }
   CUtensorMap ma, mb;
   int rc;
@@ -549,9 +640,15 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     rc = make_tmap_2d_bf16(&ma, A, K, M, lda, GEMM_BK, 64);
   if (rc) return rc;
   if (!b_mn)
-    rc = make_tmap_2d_bf16(&mb, B, N, K, ldb, BN, 64);
+    rc = make_tmap_2d_bf16(&mb, B, N, K, ldb, BN / CTAS, 64);
   else
     rc = make_tmap_2d_bf16(&mb, B, K, N, ldb, GEMM_BK, 64);
+  if (rc) return rc;
+  // outputs: 32-row x 64-column boxes, one per epilogue warp and 64-column chunk
+  CUtensorMap md, md2;
+  rc = make_tmap_2d_bf16(&md, D, M, N, ldd, 32, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&md2, D2 ? D2 : D, M, N, ldd, 32, 64);
   if (rc) return rc;
 
   GemmParams p;
@@ -597,7 +694,11 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     if (ga.pf_rows > 0 && ((ga.pf_cols % 8) || (ga.pf_flat_off % 8) || (ga.pf_rows + 31) / 32 > 1024)) return -2;
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  int rc2 = (BN == 256) ? launch_gemm<256>(ma, mb, p, max_ctas, s) : launch_gemm<128>(ma, mb, p, max_ctas, s);
+  int rc2;
+  if (CTAS == 2)
+    rc2 = (BN == 256) ? launch_gemm<256, 2>(ma, mb, md, md2, p, max_ctas, s) : launch_gemm<128, 2>(ma, mb, md, md2, p, max_ctas, s);
+  else
+    rc2 = (BN == 256) ? launch_gemm<256, 1>(ma, mb, md, md2, p, max_ctas, s) : launch_gemm<128, 1>(ma, mb, md, md2, p, max_ctas, s);
   if (rc2 == 0 && ga.ws > 0) {
     gather_epoch_bump_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(ga.epoch));
     rc2 = static_cast<int>(cudaGetLastError());

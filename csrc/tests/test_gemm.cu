@@ -188,6 +188,14 @@ int main(int argc, char** argv) {
       {200, 136, 72, 0, 0, B200_EPI_BIAS_GELU, 128},
       {200, 136, 72, 0, 1, B200_EPI_DGELU, 128},
       {200, 136, 72, 1, 1, B200_EPI_BIAS_RESID, 128},
+      {256, 256, 512, 0, 0, B200_EPI_BIAS, 2128},
+      {512, 512, 256, 0, 0, B200_EPI_BIAS, 2256},
+      {512, 384, 192, 0, 1, B200_EPI_NONE, 2128},
+      {512, 512, 192, 1, 1, B200_EPI_ACCUM, 2256},
+      {328, 264, 72, 0, 0, B200_EPI_BIAS_GELU, 2256},
+      {2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 2256},
+      {2048, 1024, 4096, 0, 1, B200_EPI_DGELU, 2128},
+      {4096, 1024, 2048, 1, 1, B200_EPI_NONE, 2256},
       {2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 0},
       {2048, 1024, 4096, 0, 0, B200_EPI_BIAS_RESID, 0},
       {2048, 4096, 1024, 0, 0, B200_EPI_BIAS_GELU, 0},
@@ -200,6 +208,17 @@ int main(int argc, char** argv) {
   printf("== gemm numerics: %d failing case(s) ==\n", fails);
   if (argc > 1) {
     printf("== gemm timing ==\n");
+    time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 0, "qkv fwd (auto)");
+    time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 2128, "qkv fwd pair");
+    time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 2256, "qkv fwd pair");
+    time_case(2048, 1024, 4096, 0, 0, B200_EPI_BIAS_RESID, 2128, "fc2 fwd pair");
+    time_case(2048, 1024, 4096, 0, 0, B200_EPI_BIAS_RESID, 2256, "fc2 fwd pair");
+    time_case(2048, 4096, 1024, 0, 0, B200_EPI_BIAS_GELU, 2256, "fc1 fwd pair");
+    time_case(2048, 4096, 1024, 0, 1, B200_EPI_DGELU, 2256, "fc2 dgrad pair");
+    time_case(4096, 1024, 2048, 1, 1, B200_EPI_NONE, 2128, "fc1 wgrad pair");
+    time_case(4096, 1024, 2048, 1, 1, B200_EPI_NONE, 2256, "fc1 wgrad pair");
+    time_case(8192, 8192, 8192, 0, 0, B200_EPI_NONE, 2256, "square 8k pair");
+    time_case(2048, 32000, 1024, 0, 0, B200_EPI_NONE, 2256, "lm_head fwd pair");
     time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 128, "qkv fwd");
     time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 256, "qkv fwd");
     time_case(2048, 1024, 1024, 0, 0, B200_EPI_BIAS_RESID, 128, "proj fwd");

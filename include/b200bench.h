@@ -27,7 +27,8 @@ extern "C" {
 
 /* D[M,N] = epi(A * B^T), tcgen05/TMEM/TMA.  a_mn / b_mn: 0 = operand stored [rows, K]
  * (K-major), 1 = stored [K, rows] (MN-major).  lda/ldb/ldd in elements, multiples of 8.
- * bn_hint: 128, 256 or 0 (auto).  max_ctas: 0 = one CTA per SM, else caps the persistent grid
+ * bn_hint: 0 (auto), 128 / 256 (single-CTA tile width) or 2128 / 2256 (CTA-pair cta_group::2 mode,
+ * 256 x 128 / 256 x 256 tiles per pair).  max_ctas: 0 = one CTA per SM, else caps the persistent grid
  * (used to leave SMs free for an overlapped communication kernel).
  * Replaces cuBLAS under nn.Linear / MultiheadAttention projections (TH:58,113-123,127). */
 int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int lda, int ldb,
