@@ -140,6 +140,7 @@ class NativeEngine:
         self.dres = e(M, d)
         self.dmid = e(M, d)
         self.dln = e(M, d)
+        self.dln2 = e(M, d)          # LN2's input gradient gets its own buffer (the side stream reads it late)
         self.dy_drop = e(M, d)
         self.dbig = e(M, 4 * d)
         self.dqkv = e(M, 3 * d)
@@ -149,6 +150,11 @@ class NativeEngine:
         sbytes = max(self.ops.colreduce_scratch_bytes(M, 4 * d, 1), self.ops.colreduce_scratch_bytes(M, d, 2),
                      self.ops.colreduce_scratch_bytes(M, 3 * d, 1))
         self.scratch = torch.zeros(sbytes // 4 + 64, dtype=torch.float32, device=dev)   # counters start at 0
+        self.scratch_side = torch.zeros(sbytes // 4 + 64, dtype=torch.float32, device=dev)
+        # weight-gradient GEMMs and bias / LayerNorm-parameter reductions do not feed the backward chain:
+        # they run on a side stream and fill the tail bubbles of the dgrad -> attention -> LN kernels
+        self.side = torch.cuda.Stream(device=dev)
+        self.overlap_wgrad = True
         self.seed_base = seed
         self.step_seed = torch.full((1,), seed, dtype=torch.int32, device=dev)
         self.ops.step_seed_register(self.step_seed)
@@ -281,6 +287,27 @@ class NativeEngine:
                         self.statf[0], self.statf[1])
         o.linear_fwd(self.lnf, P["transformer.wte.weight"], self.logits)
 
+    def _on_side(self, fn):
+        """Run ``fn`` (kernels that only produce parameter gradients) on the side stream, ordered after
+        everything issued so far on the current stream."""
+        if not self.overlap_wgrad:
+            fn(self.scratch)
+            return None
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.side.wait_event(ev)
+        with torch.cuda.stream(self.side):
+            fn(self.scratch_side)
+        done = torch.cuda.Event()
+        done.record(self.side)
+        return done
+
+    def _join_side(self) -> None:
+        if self.overlap_wgrad:
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+            torch.cuda.current_stream().wait_event(ev)
+
     def _loss_and_backward(self, first_micro: bool, last_micro: bool) -> None:
         o, P, G, p = self.ops, self.P, self.G, self.dropout
         reduce_now = self.comm is not None and self.strategy == "ddp" and last_micro
@@ -290,8 +317,8 @@ class NativeEngine:
                         grad_scale=1.0 / self.accum, write_grad=True)
         wte = P["transformer.wte.weight"]
         # lm_head: dlnf = dlogits @ wte ; dwte (+)= dlogits^T @ lnf      (tied weight)
+        self._on_side(lambda sc: o.linear_wgrad(self.logits, self.lnf, G["transformer.wte.weight"], accumulate=acc))
         o.linear_dgrad(self.logits, wte, self.dln)
-        o.linear_wgrad(self.logits, self.lnf, G["transformer.wte.weight"], accumulate=acc)
         o.layernorm_bwd(self.dln, self.x[self.L], P["transformer.ln_f.weight"], self.statf[0], self.statf[1],
                         self.dres)
         o.layernorm_bwd_params(self.dln, self.x[self.L], self.statf[0], self.statf[1],
@@ -299,42 +326,51 @@ class NativeEngine:
         for l in reversed(range(self.L)):
             pre = f"transformer.h.{l}."
             st = self.stats[l]
+            # every buffer the side stream read for block l+1 is about to be overwritten
+            self._join_side()
             # ---- MLP ----
             dy = self.dres
             if p > 0:
                 o.dropout_apply(self.dres, self.dy_drop, M, d, p, self._seed(l, 2))
                 dy = self.dy_drop
-            o.colsum(dy, G[pre + "mlp.2.bias"], self.scratch, acc)
-            o.linear_wgrad(dy, self.act[l], G[pre + "mlp.2.weight"], accumulate=acc)
+            dy_read = self._on_side(lambda sc, dy=dy: (o.colsum(dy, G[pre + "mlp.2.bias"], sc, acc),
+                                                       o.linear_wgrad(dy, self.act[l], G[pre + "mlp.2.weight"],
+                                                                      accumulate=acc)))
             w, g = self._w(pre + "mlp.2.weight")
             o.linear_dgrad(dy, w, self.dbig, epi=_ops.EPI_DGELU, aux=self.pre[l], gather=g)
-            o.colsum(self.dbig, G[pre + "mlp.0.bias"], self.scratch, acc)
-            o.linear_wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc)
+            self._on_side(lambda sc: (o.colsum(self.dbig, G[pre + "mlp.0.bias"], sc, acc),
+                                      o.linear_wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc)))
             w, g = self._w(pre + "mlp.0.weight")
-            o.linear_dgrad(self.dbig, w, self.dln, gather=g)
-            o.layernorm_bwd(self.dln, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid, dres=self.dres)
-            o.layernorm_bwd_params(self.dln, self.xmid[l], st[2], st[3], G[pre + "ln_2.weight"],
-                                   G[pre + "ln_2.bias"], self.scratch, acc)
+            o.linear_dgrad(self.dbig, w, self.dln2, gather=g)
+            o.layernorm_bwd(self.dln2, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid, dres=self.dres)
             # ---- attention ----
-            o.colsum(self.dmid, G[pre + "attn.out_proj.bias"], self.scratch, acc)
-            o.linear_wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"], accumulate=acc)
+            self._on_side(lambda sc: (o.layernorm_bwd_params(self.dln2, self.xmid[l], st[2], st[3],
+                                                             G[pre + "ln_2.weight"], G[pre + "ln_2.bias"], sc, acc),
+                                      o.colsum(self.dmid, G[pre + "attn.out_proj.bias"], sc, acc),
+                                      o.linear_wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"],
+                                                     accumulate=acc)))
             w, g = self._w(pre + "attn.out_proj.weight")
             o.linear_dgrad(self.dmid, w, self.datt, gather=g)
             o.attention_bwd(self.qkv[l], self.att[l], self.datt, self.lse[l], self.dqkv, self.attD, self.dq_acc,
                             B, T, H, hd, self.causal, p, self._seed(l, 1))
-            o.colsum(self.dqkv, G[pre + "attn.in_proj_bias"], self.scratch, acc)
-            o.linear_wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"], accumulate=acc)
+            self._on_side(lambda sc: (o.colsum(self.dqkv, G[pre + "attn.in_proj_bias"], sc, acc),
+                                      o.linear_wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"],
+                                                     accumulate=acc)))
             w, g = self._w(pre + "attn.in_proj_weight")
             o.linear_dgrad(self.dqkv, w, self.dln, gather=g)
+            if dy is self.dres and dy_read is not None:      # no dropout: the side stream read dres itself
+                torch.cuda.current_stream().wait_event(dy_read)
             o.layernorm_bwd(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres, dres=self.dmid)
-            o.layernorm_bwd_params(self.dln, self.x[l], st[0], st[1], G[pre + "ln_1.weight"],
-                                   G[pre + "ln_1.bias"], self.scratch, acc)
+            self._on_side(lambda sc: o.layernorm_bwd_params(self.dln, self.x[l], st[0], st[1], G[pre + "ln_1.weight"],
+                                                            G[pre + "ln_1.bias"], sc, acc))
             if reduce_now:
                 # K13: this block's matrix gradients are final -> all-reduce them on the comm stream
                 # while the compute stream continues with block l-1 (overlap with backward)
+                self._join_side()
                 a, b = self.layout.layer_range(l)
                 self.comm.fork()
                 self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
+        self._join_side()       # lm_head wgrad must land before the embedding scatter-add onto the tied weight
         o.embedding_bwd(self.tokens, self.dres, G["transformer.wte.weight"], G["transformer.wpe.weight"],
                         B, T, d, p, self._seed(-1, 0), accumulate_wpe=acc)
         if reduce_now:
@@ -460,25 +496,47 @@ class NativeEngine:
         self._launches_per_step = eager + (self._graph_launches if self._graphs else 0)
         return self.loss
 
-    def profile_breakdown(self) -> Dict[str, float]:
-        """Per-phase device times (ms) of one optimizer step, run eagerly with CUDA events between the
-        phases (the reference has no profiling hooks).  Call between training steps, on an
-        accumulation boundary.  The step is a real one: weights are updated."""
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        if self.dropout > 0:
-            self.ops.step_seed_advance()
-        self._gseq = 0
-        ev[0].record()
-        self._forward()
-        ev[1].record()
-        self._loss_and_backward(True, True)      # includes the overlapped DDP all-reduces and their join
-        ev[2].record()
-        self.micro = 0
-        self._optimizer_boundary()
-        ev[3].record()
+    def profile_breakdown(self, reps: int = 5) -> Dict[str, float]:
+        """Per-phase device times (ms) of one optimizer step (the reference has no profiling
+        hooks).  Forward, loss+backward and the optimizer boundary are each captured into their own CUDA
+        graph and replayed ``reps`` times between CUDA events, so the numbers carry no Python launch
+        overhead.  Call between training steps on an accumulation boundary; the replays are real work
+        (weights move by ``reps`` optimizer steps) and ranks must call it together."""
+        def timed(fn) -> float:
+            fn()                                      # warm (also keeps lazy init out of the capture)
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize(self.device)
+            return e0.elapsed_time(e1) / reps
+
+        def fwd():
+            self._gseq = 0
+            self._forward()
+
+        def bwd():
+            self._gseq = 4 * self.L if self.sharded_params else 0
+            self._loss_and_backward(True, True)
+
+        out = {"forward_ms": timed(fwd)}
+        if self.sharded_params:
+            fwd()                                     # leave the prefetch chain where backward expects it
+        out["backward_ms"] = timed(bwd)
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        self._optimizer_boundary()                    # eager: a handful of launches, host cost is negligible
+        t1.record()
         torch.cuda.synchronize(self.device)
-        out = {"forward_ms": ev[0].elapsed_time(ev[1]), "backward_ms": ev[1].elapsed_time(ev[2]),
-               "optimizer_and_comm_ms": ev[2].elapsed_time(ev[3]), "total_ms": ev[0].elapsed_time(ev[3])}
+        out["optimizer_and_comm_ms"] = t0.elapsed_time(t1)
+        out["total_ms"] = sum(out.values())
+        self.micro = 0
         return {k: round(v, 3) for k, v in out.items()}
 
     # ---------------------------------------------------------------------------------------

@@ -215,8 +215,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
 
     // One (key block, query block) tile for this thread's key row and its 64 query columns.
     // EDGE (compile-time) adds the sequence-tail / causal predicates; interior tiles carry none.
-    auto tile_body = [&](auto edge_c, int q0) {
+    auto tile_body = [&](auto edge_c, auto drop_c, int q0) {
       constexpr bool EDGE = decltype(edge_c)::value;
+      constexpr bool DROP = decltype(drop_c)::value;
       const bool row_ok = krow < p.T;
       const int q_lo = p.causal ? krow : 0;   // valid queries: q_lo <= q < T
       uint32_t vs[2][32], vd[2][32];
@@ -236,6 +237,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
           const float4 l4 = *reinterpret_cast<const float4*>(sLSE + col0 + e4);
           const float4 d4 = *reinterpret_cast<const float4*>(sD + col0 + e4);
           const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, dd[4] = {d4.x, d4.y, d4.z, d4.w};
+          uint32_t kk[4] = {0, 0, 0, 0};
+          if (DROP) {
+            const uint4 k4 = *reinterpret_cast<const uint4*>(sKey + col0 + e4);
+            kk[0] = k4.x; kk[1] = k4.y; kk[2] = k4.z; kk[3] = k4.w;
+          }
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
             const int e = e4 + t;
@@ -244,27 +250,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
               const int q = q0 + col0 + e;
               pv = (row_ok && q < p.T && q >= q_lo) ? pv : 0.f;
             }
-            pt[e] = pv;
-            ds[e] = pv * (__uint_as_float(vd[c][e]) - dd[t]);
-          }
-        }
-        if (drop) {
-#pragma unroll
-          for (int e4 = 0; e4 < 32; e4 += 4) {
-            const uint4 k4 = *reinterpret_cast<const uint4*>(sKey + col0 + e4);
-            const uint32_t kk[4] = {k4.x, k4.y, k4.z, k4.w};
-#pragma unroll
-            for (int t = 0; t < 4; ++t) {
-              const int e = e4 + t;
-              const uint32_t bits = (drop_mix(kk[t] + kpair) >> kshift) & 0xFFFFu;
-              const bool keep = bits >= thr16;
-              // dS = P * (keep ? dP/(1-p) : 0 - D);  P_drop feeds dV
-              const float pv = pt[e];
-              const float dpd = keep ? __uint_as_float(vd[c][e]) * p.drop_scale : 0.f;
-              const float dcol = *(sD + col0 + e);
-              ds[e] = pv * (dpd - dcol);
-              pt[e] = keep ? pv * p.drop_scale : 0.f;
+            float dp = __uint_as_float(vd[c][e]);
+            float pd = pv;
+            if (DROP) {
+              // dS = P * (keep ? dP/(1-p) : 0 - D);  the dropped-and-rescaled P feeds dV
+              const bool keep = ((drop_mix(kk[t] + kpair) >> kshift) & 0xFFFFu) >= thr16;
+              dp = keep ? dp * p.drop_scale : 0.f;
+              pd = keep ? pv * p.drop_scale : 0.f;
             }
+            pt[e] = pd;
+            ds[e] = pv * (dp - dd[t]);
           }
         }
 #pragma unroll
@@ -304,27 +299,39 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       mbar_arrive(dq_empty);
     };
 
+    // per-query statistics of block qi for this thread: LSE (threads 0..127) or D (threads 128..255)
+    auto load_stat = [&](int qi) -> float {
+      const int q = qi * AB_BLK + (tid & (AB_BLK - 1));
+      if (qi >= nblk || q >= p.T) return 0.f;
+      return (tid < AB_BLK) ? p.lse[static_cast<size_t>(bh) * p.T + q] : p.D[static_cast<size_t>(bh) * p.T + q];
+    };
+    float pre_val = load_stat(i_begin);
+
     for (int i = i_begin; i < nblk; ++i) {
       const int q0 = i * AB_BLK;
       const int buf = (i - i_begin) & 1;
       rowP = sP + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
       rowS = sDS + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
-      // stage LSE (times log2e), D and the dropout row keys for the 128 queries of this block
+      // stage LSE (times log2e), D and the dropout row keys for the 128 queries of this block; the
+      // global loads were issued one iteration ahead (pre_val), so nobody stalls on them here
       if (tid < AB_BLK) {
-        const int q = q0 + tid;
-        sLSE[tid] = (q < p.T) ? p.lse[static_cast<size_t>(bh) * p.T + q] * 1.4426950408889634f : 0.f;
+        sLSE[tid] = pre_val * 1.4426950408889634f;
       } else {
-        const int q = q0 + tid - AB_BLK;
-        sD[tid - AB_BLK] = (q < p.T) ? p.D[static_cast<size_t>(bh) * p.T + q] : 0.f;
-        if (drop) sKey[tid - AB_BLK] = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + q);
+        sD[tid - AB_BLK] = pre_val;
+        if (drop) sKey[tid - AB_BLK] = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + q0 + tid - AB_BLK);
       }
+      pre_val = load_stat(i + 1);
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(sdp_full, it_ph);
       tc_fence_after();
       // buffer (i & 1) was last read by the products of block i-2, whose completion (dq_full) every
       // thread observed when it drained dQ(i-2) during the previous iteration
       const bool edge = (k0 + AB_BLK > p.T) || (q0 + AB_BLK > p.T) || (p.causal && i == jb);
-      if (edge) tile_body(std::true_type{}, q0); else tile_body(std::false_type{}, q0);
+      if (drop) {
+        if (edge) tile_body(std::true_type{}, std::true_type{}, q0); else tile_body(std::false_type{}, std::true_type{}, q0);
+      } else {
+        if (edge) tile_body(std::true_type{}, std::false_type{}, q0); else tile_body(std::false_type{}, std::false_type{}, q0);
+      }
       asm volatile("bar.sync 1, 256;" ::: "memory");   // everyone is done with sLSE / sD / sKey
       tc_fence_before();
       fence_proxy_async();
