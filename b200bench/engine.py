@@ -155,6 +155,9 @@ class NativeEngine:
         # they run on a side stream and fill the tail bubbles of the dgrad -> attention -> LN kernels
         self.side = torch.cuda.Stream(device=dev)
         self.overlap_wgrad = True
+        # ddp without clipping: AdamW of a block runs as soon as its gradients are final (memory-bound, it
+        # hides behind the compute-bound backward of the earlier blocks); the boundary has nothing left to do
+        self.opt_in_backward = strategy == "ddp" and not (cfg.optim.grad_clip > 0)
         self.seed_base = seed
         self.step_seed = torch.full((1,), seed, dtype=torch.int32, device=dev)
         self.ops.step_seed_register(self.step_seed)
@@ -302,6 +305,10 @@ class NativeEngine:
         done.record(self.side)
         return done
 
+    def _adamw_range(self, a: int, b: int) -> None:
+        self.ops.adamw_flat(self.master[a:b], self.exp_avg[a:b], self.exp_avg_sq[a:b], self.grads[a:b],
+                            self.params[a:b], self.hp)
+
     def _join_side(self) -> None:
         if self.overlap_wgrad:
             ev = torch.cuda.Event()
@@ -311,6 +318,7 @@ class NativeEngine:
     def _loss_and_backward(self, first_micro: bool, last_micro: bool) -> None:
         o, P, G, p = self.ops, self.P, self.G, self.dropout
         reduce_now = self.comm is not None and self.strategy == "ddp" and last_micro
+        opt_now = self.opt_in_backward and last_micro and (self.comm is not None or self.ctx.world_size == 1)
         B, T, d, H, hd, M, V = self.B, self.T, self.d, self.H, self.hd, self.M, self.V
         acc = not first_micro
         o.cross_entropy(self.logits, self.targets, self.loss_rows, self.n_valid, self.loss, M, V,
@@ -363,13 +371,19 @@ class NativeEngine:
             o.layernorm_bwd(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres, dres=self.dmid)
             self._on_side(lambda sc: o.layernorm_bwd_params(self.dln, self.x[l], st[0], st[1], G[pre + "ln_1.weight"],
                                                             G[pre + "ln_1.bias"], sc, acc))
+            a, b = self.layout.layer_range(l)
             if reduce_now:
                 # K13: this block's matrix gradients are final -> all-reduce them on the comm stream
                 # while the compute stream continues with block l-1 (overlap with backward)
                 self._join_side()
-                a, b = self.layout.layer_range(l)
                 self.comm.fork()
                 self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
+                if opt_now:
+                    with torch.cuda.stream(self.comm.stream):
+                        self._adamw_range(a, b)
+            elif opt_now:
+                # single GPU: the block's wgrads were just queued on the side stream; its AdamW follows them
+                self._on_side(lambda sc: self._adamw_range(a, b))
         self._join_side()       # lm_head wgrad must land before the embedding scatter-add onto the tied weight
         o.embedding_bwd(self.tokens, self.dres, G["transformer.wte.weight"], G["transformer.wpe.weight"],
                         B, T, d, p, self._seed(-1, 0), accumulate_wpe=acc)
@@ -377,7 +391,14 @@ class NativeEngine:
             self.comm.fork()
             for a, b in (self._bucket_tail, self._bucket_head):
                 self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
+                if opt_now:
+                    with torch.cuda.stream(self.comm.stream):
+                        self._adamw_range(a, b)
             self.comm.join()
+        elif opt_now:
+            for a, b in (self._bucket_tail, self._bucket_head):
+                self._adamw_range(a, b)
+            self._join_side()
 
     # ---------------------------------------------------------------------------------------
     def _micro_step(self, first_micro: bool, last_micro: bool) -> None:
@@ -451,6 +472,8 @@ class NativeEngine:
 
     def _optimizer_boundary(self) -> None:
         ctx, ws = self.ctx, self.ctx.world_size
+        if self.opt_in_backward and (self.comm is not None or ws == 1):
+            return                              # already applied block by block during backward
         scale = 1.0 / ws
         clip = self.cfg.optim.grad_clip > 0
         if self.comm is not None:
@@ -488,6 +511,8 @@ class NativeEngine:
         first = (self.micro % self.accum) == 0
         last = ((self.micro + 1) % self.accum) == 0
         before = self.ops.launches
+        if last and self.opt_in_backward and (self.comm is not None or self.ctx.world_size == 1):
+            self._set_hp(1.0)                   # K13 already scaled the gradients by 1/N
         self._run_micro(first, last)
         self.micro += 1
         if last:
@@ -524,6 +549,8 @@ class NativeEngine:
             self._gseq = 4 * self.L if self.sharded_params else 0
             self._loss_and_backward(True, True)
 
+        if self.opt_in_backward:
+            self._set_hp(1.0)                     # the block-wise AdamW launches inside backward read it
         out = {"forward_ms": timed(fwd)}
         if self.sharded_params:
             fwd()                                     # leave the prefetch chain where backward expects it
