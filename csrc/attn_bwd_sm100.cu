@@ -206,9 +206,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     const uint32_t t_lane = static_cast<uint32_t>(quarter * 32) << 16;
     const int tid = threadIdx.x - 128;   // 0..255
     const bool drop = p.drop_threshold != 0;
-    const uint32_t thr16 = p.drop_threshold;
-    const uint32_t kpair = static_cast<uint32_t>(krow >> 1);
-    const uint32_t kshift = (krow & 1) ? 0u : 16u;
+    const uint32_t thr32 = p.drop_threshold;   // p * 2^32
+    const uint32_t colkey = drop_colkey(seed, static_cast<uint32_t>(bh) * p.T + krow);   // b(k) of this thread's key
     uint8_t* rowP = nullptr;   // set per query block: P/dS buffer (i & 1)
     uint8_t* rowS = nullptr;
     uint32_t it_ph = 0;
@@ -254,7 +253,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
             float pd = pv;
             if (DROP) {
               // dS = P * (keep ? dP/(1-p) : 0 - D);  the dropped-and-rescaled P feeds dV
-              const bool keep = ((drop_mix(kk[t] + kpair) >> kshift) & 0xFFFFu) >= thr16;
+              const bool keep = drop_keep2d(kk[t], colkey, thr32);
               dp = keep ? dp * p.drop_scale : 0.f;
               pd = keep ? pv * p.drop_scale : 0.f;
             }
@@ -465,8 +464,8 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   p.scale_log2 = p.scale * 1.4426950408889634f;
   p.causal = causal;
   if (drop_p > 0.f && drop_p < 1.f) {
-    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 65536.0 + 0.5);  // 16-bit
-    p.drop_scale = 1.f / (1.f - p.drop_threshold / 65536.f);
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
+    p.drop_scale = 1.f / (1.f - drop_p);
   } else {
     p.drop_threshold = 0;
     p.drop_scale = 1.f;

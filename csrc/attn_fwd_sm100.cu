@@ -39,8 +39,8 @@ constexpr int AT_KV_STAGES = 3;
 constexpr int AT_THREADS = 384;  // warpgroup 0: TMA + MMA (+2 idle warps), warpgroups 1-2: softmax
 constexpr int AT_TILE = AT_BN * AT_HD * 2;   // 16 KiB: one [128 x 64] bf16 tile
 constexpr int AT_PBYTES = AT_BM * AT_BN * 2; // 32 KiB: one P buffer
-constexpr int AT_SMEM = AT_TILE * (1 + 2 * AT_KV_STAGES) + 2 * AT_PBYTES + 1024 /*bars+merge*/ +
-                        1024 /*align*/;
+constexpr int AT_SMEM = AT_TILE * (1 + 2 * AT_KV_STAGES) + 2 * AT_PBYTES + 1280 /*bars+merge*/ +
+                        2048 /*dropout column keys: 2 warpgroups x 2 buffers x 128*/;
 constexpr float NEG_BIG = -1.0e30f;
 
 struct AttnFwdParams {
@@ -76,6 +76,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
   uint64_t* o_full = bars + 17;                    // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
   float* merge_ml = reinterpret_cast<float*>(bars + 20);  // [2][128] m, l of warpgroup 1
+  uint32_t* sColKey = reinterpret_cast<uint32_t*>(merge_ml + 256);   // [2 warpgroups][2 buffers][128]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qblocks = (p.T + AT_BM - 1) / AT_BM;
@@ -225,12 +226,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
 
     const uint32_t rowkey = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + qrow);
     const bool drop = p.drop_threshold != 0;
-    const uint32_t thr16 = p.drop_threshold;   // 16-bit threshold (see host wrapper)
+    const uint32_t thr32 = p.drop_threshold;   // p * 2^32
 
     // One key block for this thread's query row.  MASK is a compile-time flag so that the common
     // (interior, non-causal) blocks carry no per-element predicate; limit = first masked key.
     auto block_body = [&](auto mask_c, int k0, int limit) {
       constexpr bool MASK = decltype(mask_c)::value;
+      const uint32_t* colkeys = sColKey + (w * 2 + (n_done & 1)) * 128;
+      if (drop) {
+        // b(k) for the 128 keys of this block, one per thread; double-buffered by block parity so one
+        // warpgroup barrier per block is enough
+        sColKey[(w * 2 + (n_done & 1)) * 128 + r] = drop_colkey(seed, static_cast<uint32_t>(bh) * p.T + k0 + r);
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + w) : "memory");
+      }
       // ---- pass 1: row maximum (4 independent chains, two 64-column loads) ----------------
       float mx[4] = {NEG_BIG, NEG_BIG, NEG_BIG, NEG_BIG};
 #pragma unroll 1
@@ -272,12 +280,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
           pv[i] = e;
         }
         if (drop) {
-          const uint32_t kp = rowkey + static_cast<uint32_t>((k0 + c * 32) >> 1);
 #pragma unroll
-          for (int t = 0; t < 16; ++t) {
-            const uint32_t wd = drop_mix(kp + t);
-            pv[2 * t] = ((wd >> 16) >= thr16) ? pv[2 * t] * p.drop_scale : 0.f;
-            pv[2 * t + 1] = ((wd & 0xFFFFu) >= thr16) ? pv[2 * t + 1] * p.drop_scale : 0.f;
+          for (int t4 = 0; t4 < 32; t4 += 4) {
+            const uint4 b4 = *reinterpret_cast<const uint4*>(colkeys + c * 32 + t4);
+            pv[t4 + 0] = drop_keep2d(rowkey, b4.x, thr32) ? pv[t4 + 0] * p.drop_scale : 0.f;
+            pv[t4 + 1] = drop_keep2d(rowkey, b4.y, thr32) ? pv[t4 + 1] * p.drop_scale : 0.f;
+            pv[t4 + 2] = drop_keep2d(rowkey, b4.z, thr32) ? pv[t4 + 2] * p.drop_scale : 0.f;
+            pv[t4 + 3] = drop_keep2d(rowkey, b4.w, thr32) ? pv[t4 + 3] * p.drop_scale : 0.f;
           }
         }
         // 32 keys = 4 x 16-byte chunks of the 128-byte swizzled row; chunk index XOR (row & 7)
@@ -392,8 +401,8 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B,
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(head_dim));
   p.causal = causal;
   if (drop_p > 0.f && drop_p < 1.f) {
-    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 65536.0 + 0.5);  // 16-bit
-    p.drop_scale = 1.f / (1.f - p.drop_threshold / 65536.f);
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(drop_p) * 4294967296.0);
+    p.drop_scale = 1.f / (1.f - drop_p);
   } else {
     p.drop_threshold = 0;
     p.drop_scale = 1.f;

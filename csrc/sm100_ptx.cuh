@@ -362,6 +362,17 @@ __device__ __forceinline__ uint32_t drop_mix(uint32_t x) {
   x ^= x >> 16;
   return x;
 }
+// Cheapest form, used by the attention kernels: a 2-D decomposable hash.  Each query row q gets a key
+// a(q) and each key column k a key b(k) (both full-strength hashes, computed once per 128-block); the
+// per-element decision is a single multiply:  keep(q,k) = ((a(q) ^ b(k)) * 0x9E3779B1) >= p * 2^32.
+// Forward (thread = query row, walks keys) and backward (thread = key row, walks queries) both get it
+// for ~2 ALU ops per element and always agree.
+__device__ __forceinline__ uint32_t drop_colkey(uint32_t seed, uint32_t col_index) {
+  return hash_u32((seed ^ 0x5bd1e995U) + hash_u32(col_index + 0x85ebca6bU));
+}
+__device__ __forceinline__ bool drop_keep2d(uint32_t a, uint32_t b, uint32_t thr32) {
+  return ((a ^ b) * 0x9E3779B1U) >= thr32;
+}
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
 }
