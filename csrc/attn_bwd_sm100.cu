@@ -114,6 +114,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();   // dependents may start their prologue; they wait for this grid's completion themselves
+  pdl_wait();      // nothing below may run before the previous kernel's writes are visible
   constexpr uint32_t TC_S = 0, TC_DP = 128, TC_DV = 256, TC_DK = 320, TC_DQ = 384;
 
   if (warp < 4) {
@@ -473,7 +475,20 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
   p.drop_seed = seed;
   p.seed_ptr = step_seed_ptr();
   const int grid = B * H * ((T + AB_BLK - 1) / AB_BLK);
-  attn_bwd_kernel<<<grid, AB_THREADS, AB_SMEM, s>>>(map_qkv, map_do, p);
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(AB_THREADS);
+    cfg.dynamicSmemBytes = AB_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // PDL: prologue overlaps the prep kernel's tail
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, attn_bwd_kernel, map_qkv, map_do, p);
+    if (le != cudaSuccess) return static_cast<int>(le);
+  }
   {
     const size_t work = static_cast<size_t>(M) * (d / 8);
     size_t blocks = (work + 255) / 256;

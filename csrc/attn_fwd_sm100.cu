@@ -109,6 +109,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();   // dependents may start their prologue; they wait for this grid's completion themselves
+  pdl_wait();      // nothing below may run before the previous kernel's writes are visible
   // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384)
 
   if (warp < 4) {
@@ -410,6 +412,15 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B,
   p.drop_seed = seed;
   p.seed_ptr = step_seed_ptr();
   const int grid = B * H * ((T + AT_BM - 1) / AT_BM);
-  attn_fwd_kernel<<<grid, AT_THREADS, AT_SMEM, static_cast<cudaStream_t>(stream)>>>(map, p);
-  return static_cast<int>(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(AT_THREADS);
+  cfg.dynamicSmemBytes = AT_SMEM;
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // PDL: prologue overlaps the previous kernel's tail
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, attn_fwd_kernel, map, p));
 }

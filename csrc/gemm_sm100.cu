@@ -163,6 +163,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   if (CTAS == 2) cluster_sync_all();   // the peer's barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the tail of the
+  // previous kernel in the stream; nothing below may start before that kernel's writes are visible.
+  pdl_trigger();
+  pdl_wait();
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -541,6 +545,8 @@ int device_sm_count() {
   return sms[dev];
 }
 
+static int g_gemm_pdl = 1;   // b200_set_option("gemm_pdl", 0) turns programmatic dependent launch off
+
 template <int BN, int CTAS>
 static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md,
                        const CUtensorMap& md2, GemmParams& p, int max_ctas, cudaStream_t stream) {
@@ -569,13 +575,15 @@ static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
   cfg.blockDim = dim3(threads);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CTAS;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // PDL: see pdl_wait() in the kernel
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = g_gemm_pdl ? 2 : 1;
   return static_cast<int>(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<BN, CTAS>, ma, mb, md, md2, p));
 }
 
@@ -704,6 +712,11 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     rc2 = static_cast<int>(cudaGetLastError());
   }
   return rc2;
+}
+
+extern "C" int b200_set_gemm_pdl(int on) {
+  g_gemm_pdl = on ? 1 : 0;
+  return 0;
 }
 
 extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int lda,

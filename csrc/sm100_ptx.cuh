@@ -36,6 +36,15 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // ----------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A kernel launched with the programmatic-stream-serialization
+// attribute may start while its predecessor is still draining; it must call pdl_wait() before it
+// touches any global memory the predecessor may write (or that it will overwrite).  pdl_trigger()
+// tells the runtime that dependents of THIS grid may begin launching.
+// ----------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// ----------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

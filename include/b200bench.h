@@ -129,6 +129,9 @@ int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* fl
                        int ws, size_t lo, size_t n, float* master, float* m, float* v, void* gshard,
                        const float* hp, int push_all, float* gnorm_out, const float* extra_norm_sq,
                        int ctas, void* stream);
+/* GEMM launches use programmatic dependent launch (their prologue overlaps the previous kernel's tail;
+ * the kernel waits with griddepcontrol.wait before touching global memory).  0 turns it off. */
+int b200_set_gemm_pdl(int on);
 /* K14: the GEMM of b200_gemm_bf16 with the all-gather of its B operand fused in.  B is a weight
  * matrix [rows, cols] partitioned over ws ranks by flat offset (partition size shard_elems, B[0,0] at
  * flat_off); shard_adj[r] = rank r's partition base MINUS r*shard_elems elements, as mapped here.
