@@ -56,6 +56,7 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
                      const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int d,
                      float eps) {
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
@@ -119,6 +120,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, const __nv_bfloat16* __restrict__ dres,
                      __nv_bfloat16* __restrict__ dx, int M, int d) {
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
   if (row >= M) return;
@@ -192,6 +194,7 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __re
                  const float* __restrict__ mean, const float* __restrict__ rstd,
                  float* __restrict__ scratch, unsigned int* __restrict__ counters, int M, int N, int ld,
                  __nv_bfloat16* __restrict__ out0, __nv_bfloat16* __restrict__ out1, int accumulate) {
+  pdl_wait();
   constexpr int K = (MODE == 1) ? 2 : 1;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int col = (blockIdx.x * 32 + tx) * 8;
@@ -269,6 +272,7 @@ __global__ void __launch_bounds__(256)
 embedding_fwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restrict__ wte,
                      const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ out, int M,
                      int T, int d, uint32_t thr, float scale, uint32_t seed, const uint32_t* __restrict__ seed_ptr) {
+  pdl_wait();
   if (thr && seed_ptr) seed ^= __ldg(seed_ptr);
   const int nvec = d >> 3;
   const size_t total = static_cast<size_t>(M) * nvec;
@@ -299,6 +303,7 @@ embedding_bwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restric
                      __nv_bfloat16* __restrict__ dwte, __nv_bfloat16* __restrict__ dwpe, int B, int T,
                      int d, uint32_t thr, float scale, uint32_t seed, int accumulate_wpe,
                      const uint32_t* __restrict__ seed_ptr) {
+  pdl_wait();
   if (thr && seed_ptr) seed ^= __ldg(seed_ptr);
   const int nvec = d >> 3;
   const size_t total = static_cast<size_t>(T) * nvec;
@@ -348,6 +353,7 @@ constexpr int CE_MAXV = 8;  // uint4 per thread cached in registers: V <= 8*8*51
 
 __global__ void count_valid_kernel(const int* __restrict__ targets, int M, int ignore_index,
                                    int* __restrict__ n_valid) {
+  pdl_wait();
   __shared__ int s;
   if (threadIdx.x == 0) s = 0;
   __syncthreads();
@@ -374,6 +380,7 @@ __global__ void __launch_bounds__(CE_THREADS)
 cross_entropy_kernel(__nv_bfloat16* __restrict__ logits, const int* __restrict__ targets,
                      float* __restrict__ loss_rows, int V, int ld, int ignore_index,
                      const int* __restrict__ n_valid, float grad_scale, int write_grad) {
+  pdl_wait();
   __shared__ float sh[32];
   const int row = blockIdx.x;
   uint4* lr = reinterpret_cast<uint4*>(logits + static_cast<size_t>(row) * ld);
@@ -462,6 +469,7 @@ cross_entropy_kernel(__nv_bfloat16* __restrict__ logits, const int* __restrict__
 __global__ void ce_finalize_kernel(const float* __restrict__ loss_rows, int M,
                                    const int* __restrict__ n_valid, float* __restrict__ loss_out,
                                    int accumulate, float scale) {
+  pdl_wait();
   __shared__ float sh[32];
   float s = 0.f;
   for (int i = threadIdx.x; i < M; i += blockDim.x) s += loss_rows[i];
@@ -521,6 +529,7 @@ __global__ void __launch_bounds__(256)
 adamw_kernel(float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
              const __nv_bfloat16* __restrict__ grad, __nv_bfloat16* __restrict__ w_out, size_t n,
              const float* __restrict__ hp, const float* __restrict__ gnorm_sq) {
+  pdl_wait();
   const AdamCoef c = load_adam_coef(hp, gnorm_sq);
   const size_t nvec = n >> 3;  // 8 elements per iteration (one uint4 of bf16 grads)
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < nvec;
@@ -547,6 +556,7 @@ adamw_kernel(float* __restrict__ master, float* __restrict__ m, float* __restric
 
 __global__ void __launch_bounds__(256)
 sumsq_kernel(const __nv_bfloat16* __restrict__ g, size_t n, float scale, float* __restrict__ out) {
+  pdl_wait();
   __shared__ float sh[32];
   float s = 0.f;
   const size_t nvec = n >> 3;
@@ -565,6 +575,7 @@ __global__ void __launch_bounds__(256)
 dropout_apply_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int M,
                      int N, uint32_t thr, float scale, uint32_t seed,
                      const uint32_t* __restrict__ seed_ptr) {
+  pdl_wait();
   if (seed_ptr) seed ^= __ldg(seed_ptr);
   const int nvec = N >> 3;
   const size_t total = static_cast<size_t>(M) * nvec;
@@ -629,11 +640,11 @@ using namespace b200;
   do {                                                                            \
     const int nv = (d / 8 + 31) / 32;                                             \
     const int blocks = (M + 7) / 8;                                               \
-    if (nv <= 1) KERNEL<1><<<blocks, 256, 0, s>>>(__VA_ARGS__);                   \
-    else if (nv <= 2) KERNEL<2><<<blocks, 256, 0, s>>>(__VA_ARGS__);              \
-    else if (nv <= 4) KERNEL<4><<<blocks, 256, 0, s>>>(__VA_ARGS__);              \
-    else if (nv <= 8) KERNEL<8><<<blocks, 256, 0, s>>>(__VA_ARGS__);              \
-    else if (nv <= 16) KERNEL<16><<<blocks, 256, 0, s>>>(__VA_ARGS__);            \
+    if (nv <= 1) launch_pdl(KERNEL<1>, dim3(blocks), dim3(256), 0, s, __VA_ARGS__);                 \
+    else if (nv <= 2) launch_pdl(KERNEL<2>, dim3(blocks), dim3(256), 0, s, __VA_ARGS__);              \
+    else if (nv <= 4) launch_pdl(KERNEL<4>, dim3(blocks), dim3(256), 0, s, __VA_ARGS__);              \
+    else if (nv <= 8) launch_pdl(KERNEL<8>, dim3(blocks), dim3(256), 0, s, __VA_ARGS__);              \
+    else if (nv <= 16) launch_pdl(KERNEL<16>, dim3(blocks), dim3(256), 0, s, __VA_ARGS__);            \
     else return -3;                                                               \
   } while (0)
 
@@ -677,7 +688,7 @@ extern "C" int b200_layernorm_bwd_params(const void* dy, const void* x, const fl
   if ((d + 255) / 256 > kColreduceCounters) return -3;
   unsigned int* counters = static_cast<unsigned int*>(scratch);
   float* part = reinterpret_cast<float*>(counters + kColreduceCounters);
-  colreduce_kernel<1><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy),
+  launch_pdl(colreduce_kernel<1>, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dy),
                                            static_cast<const __nv_bfloat16*>(x), mean, rstd, part,
                                            counters, M, d, d, static_cast<__nv_bfloat16*>(dgamma),
                                            static_cast<__nv_bfloat16*>(dbeta), accumulate);
@@ -694,7 +705,7 @@ extern "C" int b200_colsum(const void* dy, void* out, int M, int N, int ld, int 
   if ((N + 255) / 256 > kColreduceCounters) return -3;
   unsigned int* counters = static_cast<unsigned int*>(scratch);
   float* part = reinterpret_cast<float*>(counters + kColreduceCounters);
-  colreduce_kernel<0><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), nullptr, nullptr,
+  launch_pdl(colreduce_kernel<0>, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dy), nullptr, nullptr,
                                            nullptr, part, counters, M, N, ld,
                                            static_cast<__nv_bfloat16*>(out), nullptr, accumulate);
   return static_cast<int>(cudaGetLastError());
@@ -707,7 +718,7 @@ extern "C" int b200_embedding_fwd(const int* tokens, const void* wte, const void
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t work = static_cast<size_t>(B) * T * (d / 8);
   const float scale = drop_p > 0.f && drop_p < 1.f ? 1.f / (1.f - drop_p) : 1.f;
-  embedding_fwd_kernel<<<grid_for(work, 256, 8), 256, 0, s>>>(
+  launch_pdl(embedding_fwd_kernel, dim3(grid_for(work, 256, 8)), dim3(256), 0, s, 
       tokens, static_cast<const __nv_bfloat16*>(wte), static_cast<const __nv_bfloat16*>(wpe),
       static_cast<__nv_bfloat16*>(out), B * T, T, d, drop_thr(drop_p), scale, seed, step_seed_ptr());
   return static_cast<int>(cudaGetLastError());
@@ -720,7 +731,7 @@ extern "C" int b200_embedding_bwd(const int* tokens, const void* dx, void* dwte,
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t work = static_cast<size_t>(T) * (d / 8);
   const float scale = drop_p > 0.f && drop_p < 1.f ? 1.f / (1.f - drop_p) : 1.f;
-  embedding_bwd_kernel<<<grid_for(work, 256, 8), 256, 0, s>>>(
+  launch_pdl(embedding_bwd_kernel, dim3(grid_for(work, 256, 8)), dim3(256), 0, s, 
       tokens, static_cast<const __nv_bfloat16*>(dx), static_cast<__nv_bfloat16*>(dwte),
       static_cast<__nv_bfloat16*>(dwpe), B, T, d, drop_thr(drop_p), scale, seed, accumulate_wpe,
       step_seed_ptr());
@@ -733,11 +744,11 @@ extern "C" int b200_cross_entropy(void* logits, const int* targets, float* loss_
                                   int accumulate_loss, float loss_scale, void* stream) {
   if ((V % 8) || (ld % 8)) return -2;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  count_valid_kernel<<<1, 1024, 0, s>>>(targets, M, ignore_index, n_valid);
-  cross_entropy_kernel<<<M, CE_THREADS, 0, s>>>(static_cast<__nv_bfloat16*>(logits), targets,
+  launch_pdl(count_valid_kernel, dim3(1), dim3(1024), 0, s, targets, M, ignore_index, n_valid);
+  launch_pdl(cross_entropy_kernel, dim3(M), dim3(CE_THREADS), 0, s, static_cast<__nv_bfloat16*>(logits), targets,
                                                 loss_rows, V, ld, ignore_index, n_valid, grad_scale,
                                                 write_grad);
-  ce_finalize_kernel<<<1, 1024, 0, s>>>(loss_rows, M, n_valid, loss_out, accumulate_loss,
+  launch_pdl(ce_finalize_kernel, dim3(1), dim3(1024), 0, s, loss_rows, M, n_valid, loss_out, accumulate_loss,
                                         loss_scale);
   return static_cast<int>(cudaGetLastError());
 }
@@ -754,7 +765,7 @@ extern "C" int b200_adamw(float* master, float* m, float* v, const void* grad, v
                           size_t n, const float* hp, const float* gnorm_sq, void* stream) {
   if (n % 8) return -2;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  adamw_kernel<<<grid_for(n / 8, 256, 8), 256, 0, s>>>(master, m, v,
+  launch_pdl(adamw_kernel, dim3(grid_for(n / 8, 256, 8)), dim3(256), 0, s, master, m, v,
                                                        static_cast<const __nv_bfloat16*>(grad),
                                                        static_cast<__nv_bfloat16*>(w_out), n, hp,
                                                        gnorm_sq);
@@ -764,7 +775,7 @@ extern "C" int b200_adamw(float* master, float* m, float* v, const void* grad, v
 extern "C" int b200_sumsq(const void* grad, size_t n, float scale, float* out, void* stream) {
   if (n % 8) return -2;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  sumsq_kernel<<<grid_for(n / 8, 256, 4), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(grad), n,
+  launch_pdl(sumsq_kernel, dim3(grid_for(n / 8, 256, 4)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(grad), n,
                                                        scale, out);
   return static_cast<int>(cudaGetLastError());
 }
@@ -780,7 +791,7 @@ extern "C" int b200_dropout_apply(const void* in, void* out, int M, int N, float
     return static_cast<int>(cudaGetLastError());
   }
   const size_t work = static_cast<size_t>(M) * (N / 8);
-  dropout_apply_kernel<<<grid_for(work, 256, 8), 256, 0, s>>>(
+  launch_pdl(dropout_apply_kernel, dim3(grid_for(work, 256, 8)), dim3(256), 0, s, 
       static_cast<const __nv_bfloat16*>(in), static_cast<__nv_bfloat16*>(out), M, N, thr,
       1.f / (1.f - drop_p), seed, step_seed_ptr());
   return static_cast<int>(cudaGetLastError());
@@ -866,7 +877,7 @@ extern "C" int b200_colsum_static(const void* dy, void* out, int M, int N, int l
   if (e != cudaSuccess) return static_cast<int>(e);
   const int R = colreduce_splits(M, N);
   dim3 grid((N + 255) / 256, R);
-  colreduce_kernel<0><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dy), nullptr, nullptr,
+  launch_pdl(colreduce_kernel<0>, dim3(grid), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(dy), nullptr, nullptr,
                                            nullptr, part, counters, M, N, ld,
                                            static_cast<__nv_bfloat16*>(out), nullptr, accumulate);
   return static_cast<int>(cudaGetLastError());
