@@ -7,7 +7,7 @@ SRCS      := $(wildcard csrc/*.cu)
 OBJS      := $(patsubst csrc/%.cu,build/obj/%.o,$(SRCS))
 HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
 LIB       := b200bench/lib/libb200bench.so
-TESTS     := build/bin/test_gemm build/bin/test_attn
+TESTS     := build/bin/test_gemm build/bin/test_attn build/bin/test_sanitize
 
 all: $(LIB) $(TESTS)
 
@@ -19,14 +19,23 @@ $(LIB): $(OBJS)
 	@mkdir -p b200bench/lib
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
 
-build/bin/%: csrc/tests/%.cu $(OBJS)
+build/bin/%: csrc/tests/%.cu $(OBJS) $(wildcard csrc/tests/*.cu)
 	@mkdir -p build/bin
 	$(NVCC) $(NVCCFLAGS) $< $(OBJS) -o $@
 
 ptxas-info:
 	@for f in $(SRCS); do echo "== $$f"; $(NVCC) $(NVCCFLAGS) -Xptxas -v -c $$f -o /dev/null 2>&1 | grep -E "registers|spill" ; done
 
+# compute-sanitizer targets (need a GPU): every single-GPU kernel at small shapes, see csrc/tests/test_sanitize.cu
+SANITIZER ?= compute-sanitizer
+memcheck: build/bin/test_sanitize
+	$(SANITIZER) --tool memcheck --error-exitcode 9 build/bin/test_sanitize
+synccheck: build/bin/test_sanitize
+	$(SANITIZER) --tool synccheck --error-exitcode 9 build/bin/test_sanitize
+initcheck: build/bin/test_sanitize
+	$(SANITIZER) --tool initcheck --error-exitcode 9 build/bin/test_sanitize
+
 clean:
 	rm -rf build b200bench/lib
 
-.PHONY: all clean ptxas-info
+.PHONY: all clean ptxas-info memcheck synccheck initcheck
