@@ -24,6 +24,7 @@ zero3   weight matrix is gathered from the owners' shards INSIDE the GEMM that c
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, Optional
 
 import torch
@@ -77,7 +78,11 @@ class NativeEngine:
         if ws > 1 and comm == "fused":
             from .parallel.peer import PeerComm
 
-            self.comm = PeerComm(ctx, device)
+            # K13 CTA count: more peers per CTA means more loads in flight per CTA, so fewer CTAs (= fewer SMs
+            # taken from the backward GEMMs) reach the same NVLink rate.  Measured: N=8 16 CTAs 9.34 ms/step,
+            # 32: 9.41, 64: 9.60 (profiles/n8*); N=2 needs 64 (profiles/comm_n2_v2.log).
+            ctas = int(os.environ.get("B200BENCH_COMM_CTAS", "0")) or {2: 64, 4: 32}.get(ws, 16)
+            self.comm = PeerComm(ctx, device, comm_ctas=ctas)
         self.sharded_params = self.comm is not None and strategy in SHARDED_PARAMS
 
         # ---- parameters / gradients ---------------------------------------------------------------
@@ -157,7 +162,8 @@ class NativeEngine:
         self.overlap_wgrad = True
         # ddp without clipping: AdamW of a block runs as soon as its gradients are final (memory-bound, it
         # hides behind the compute-bound backward of the earlier blocks); the boundary has nothing left to do
-        self.opt_in_backward = strategy == "ddp" and not (cfg.optim.grad_clip > 0)
+        self.opt_in_backward = (strategy == "ddp" and not (cfg.optim.grad_clip > 0)
+                                and os.environ.get("B200BENCH_OPT_IN_BACKWARD", "1") != "0")
         self.seed_base = seed
         self.step_seed = torch.full((1,), seed, dtype=torch.int32, device=dev)
         self.ops.step_seed_register(self.step_seed)

@@ -202,6 +202,16 @@ def run_native(a: argparse.Namespace) -> None:
             "gpu_launches": per_step * a.steps, "gpu_launches_per_step": per_step,
             "peak_vram_gb": peak / 1e9, "final_loss": float(loss_host[-1]), "impl": "native",
         })
+    if a.diag:
+        # host-side enqueue cost of a step (no sync inside) and graph-replayed phase times, every rank
+        sync_all()
+        h0 = time.perf_counter()
+        for i in range(a.steps):
+            eng.train_step(resident[i % 8], resident[i % 8])
+        host_ms = (time.perf_counter() - h0) * 1e3 / a.steps
+        sync_all()
+        phases = eng.profile_breakdown() if eng.accum == 1 else {}
+        print(f"[diag] rank {rank}: host enqueue {host_ms:.3f} ms/step, phases {phases}", file=sys.stderr, flush=True)
     eng.close()
     if ws > 1:
         dist.destroy_process_group()
@@ -220,6 +230,7 @@ def main() -> None:
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--dropout", type=float, default=0.1)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--diag", action="store_true", help="after the timed arms, print a per-phase breakdown to stderr")
     ap.add_argument("--ref-timeout", type=float, default=180.0, help="seconds before the reference arm is abandoned")
     a = ap.parse_args()
     if a.impl == "reference":
