@@ -69,6 +69,8 @@ class StrategyConfig:
     fsdp_backward_prefetch: str = "backward_pre"
     fsdp_forward_prefetch: bool = True
     fsdp_sync_module_states: bool = True
+    # "auto": keep the gathered blocks from forward to backward when they take < 5 % of device memory
+    fsdp_reshard_after_forward: Any = "auto"
     # gradient accumulation: "reference" = only ZeRO strategies honour --grad-accum
     grad_accum_mode: str = "reference"
     raw: Dict[str, Any] = field(default_factory=dict)
@@ -136,6 +138,10 @@ def load_fsdp_config(path: Optional[str]) -> StrategyConfig:
     cfg.fsdp_backward_prefetch = str(body.get("backward_prefetch", cfg.fsdp_backward_prefetch))
     cfg.fsdp_forward_prefetch = bool(body.get("forward_prefetch", cfg.fsdp_forward_prefetch))
     cfg.fsdp_sync_module_states = bool(body.get("sync_module_states", cfg.fsdp_sync_module_states))
+    r = body.get("reshard_after_forward", cfg.fsdp_reshard_after_forward)
+    if not (isinstance(r, bool) or r == "auto"):
+        raise ValueError(f"reshard_after_forward must be true, false or auto, got {r!r}")
+    cfg.fsdp_reshard_after_forward = r
     if body.get("cpu_offload", False):
         raise ValueError("cpu_offload is not supported (reference: CPUOffload(False), TH:234)")
     return cfg

@@ -53,8 +53,16 @@ class NativeEngine:
     def __init__(self, model_cfg: Dict[str, int], strategy: str, cfg: StrategyConfig, ctx: DistCtx,
                  device: torch.device, grad_accum: int = 1, dropout: float = 0.1, causal: bool = False,
                  batch: int = 1, seq_len: int = 2048, comm: str = "fused", use_graph: bool = True,
-                 seed: int = 42):
+                 seed: int = 42, param_gather: Optional[str] = None):
         self.ops = _ops.load()
+        # fsdp / zero3 weight all-gather: "gemm" = gather warps inside the consuming GEMM (K14), "stream" = one
+        # peer-gather kernel per transformer block on the comm stream, one block ahead of the compute stream
+        self.param_gather = param_gather or os.environ.get("B200BENCH_PARAM_GATHER", "stream")
+        if self.param_gather not in ("gemm", "stream"):
+            raise ValueError(f"param_gather must be 'gemm' or 'stream', got {self.param_gather!r}")
+        self.n_slots = 2
+        self._regather_tables = True
+        self._invalidate_staging()
         self.strategy, self.cfg, self.ctx, self.device = strategy, cfg, ctx, device
         self.accum = effective_grad_accum(strategy, grad_accum, cfg.grad_accum_mode)
         self.dropout, self.causal = float(dropout), bool(causal)
@@ -222,6 +230,26 @@ class NativeEngine:
         # prefetch the weight of GEMM k+1 into the other slot
         self.stage_w = torch.empty(2, 4 * self.d * self.d, dtype=BF16, device=dev)
         self.chunk_flags = torch.zeros(2, 1024, dtype=torch.int32, device=dev)
+        # "stream" mode: whole-block staging slots, block l lives in slot l % n_slots.  Two slots = gather again
+        # in backward (full re-sharding after forward).  L slots = every block stays resident until the end of the
+        # micro-step: ZeRO-3 when the model fits stage3_max_live_parameters (zero3.json:11, DeepSpeed keeps such
+        # parameters live), FSDP per reshard_after_forward (the reference's single flat unit never re-shards
+        # between forward and backward either, TH:229-237).
+        a0, a1 = Lt.layer_range(0)
+        if self.strategy == "zero3":
+            keep = Lt.big_end <= self.cfg.stage3_max_live_parameters
+        else:
+            r = self.cfg.fsdp_reshard_after_forward
+            keep = (not r) if isinstance(r, bool) else \
+                (self.L * (a1 - a0) * 2 <= 0.05 * torch.cuda.get_device_properties(dev).total_memory)
+        self.keep_gathered = bool(keep) and self.param_gather == "stream"
+        self.n_slots = self.L if self.keep_gathered else 2
+        self.gather_ctas = int(os.environ.get("B200BENCH_GATHER_CTAS", "32"))
+        self.stage_layer = (torch.empty(self.n_slots, a1 - a0, dtype=BF16, device=dev)
+                            if self.param_gather == "stream" else None)
+        self._invalidate_staging()
+        # _slot_layer: block resident (or in flight) in each slot during this micro-step; _slot_done: comm-stream
+        # event of the gather filling it; _slot_pending: the compute stream has not waited for that event yet
         order = []
         for l in range(self.L):
             order += [f"transformer.h.{l}." + k for k in BIG_SUFFIXES]
@@ -247,6 +275,12 @@ class NativeEngine:
         tells the kernel whether to gather it itself (first GEMM only) and which weight to prefetch."""
         if not self.sharded_params:
             return self.P[name], None
+        if self.param_gather == "stream":
+            s = self.layout[name]
+            a, _ = self.layout.layer_range(s.layer)
+            slot = s.layer % self.n_slots
+            assert self._slot_layer[slot] == s.layer and not self._slot_pending[slot], (name, self._slot_layer)
+            return self.stage_layer[slot][s.offset - a:s.offset - a + s.numel].view(s.shape), None
         k = self._gseq
         self._gseq += 1
         assert self._gorder[k] == name, (k, name, self._gorder[k])
@@ -261,6 +295,40 @@ class NativeEngine:
                         pf_stage=self.stage_w[1 - slot], pf_flags=self.chunk_flags[1 - slot])
         return self.stage_w[slot][:s.numel].view(s.shape), desc
 
+    def _gather_block(self, l: int) -> None:
+        """Queue the peer gather of block l's four matrices into its slot on the comm stream.  The comm
+        stream first waits for the compute stream's current position: everything that read the slot's previous
+        occupant (block l +- 2, or l itself before an optimizer step) has been queued before this call."""
+        slot = l % self.n_slots
+        a, b = self.layout.layer_range(l)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.comm.stream.wait_event(ev)
+        with torch.cuda.stream(self.comm.stream):
+            self.comm.gather_range(self.adj_table, self.stage_layer[slot], a, b - a, self.S, ctas=self.gather_ctas)
+        done = torch.cuda.Event()
+        done.record(self.comm.stream)
+        self._slot_layer[slot], self._slot_done[slot], self._slot_pending[slot] = l, done, True
+
+    def _layer_begin(self, l: int, step: int) -> None:
+        """Stream-mode prefetch schedule: make block l resident for the compute stream, then start the gather of
+        the block that comes next in this direction (step = +1 forward, -1 backward)."""
+        if not (self.sharded_params and self.param_gather == "stream"):
+            return
+        slot = l % self.n_slots
+        if self._slot_layer[slot] != l:
+            self._gather_block(l)
+        if self._slot_pending[slot]:
+            torch.cuda.current_stream().wait_event(self._slot_done[slot])
+            self._slot_pending[slot] = False
+        nxt = l + step
+        if 0 <= nxt < self.L and self._slot_layer[nxt % self.n_slots] != nxt:
+            self._gather_block(nxt)
+
+    def _invalidate_staging(self) -> None:
+        n = getattr(self, "n_slots", 2)
+        self._slot_layer, self._slot_done, self._slot_pending = [-1] * n, [None] * n, [False] * n
+
     # ---------------------------------------------------------------------------------------
     def _seed(self, layer: int, site: int) -> int:
         # The per-step component lives in device memory (graph-replay safe): see ops.step_seed_advance.
@@ -269,7 +337,7 @@ class NativeEngine:
     def _forward(self) -> None:
         o, P, p = self.ops, self.P, self.dropout
         B, T, d, H, hd = self.B, self.T, self.d, self.H, self.hd
-        if self.sharded_params:        # embedding tables: plain peer gather at the start of the micro-step
+        if self.sharded_params and self._regather_tables:   # embedding tables: plain peer gather up front
             for name, stage in (("transformer.wte.weight", self.stage_wte), ("transformer.wpe.weight", self.stage_wpe)):
                 s = self.layout[name]
                 self.comm.gather_range(self.adj_table, stage, s.offset, s.numel, self.S)
@@ -278,6 +346,7 @@ class NativeEngine:
         for l in range(self.L):
             pre = f"transformer.h.{l}."
             st = self.stats[l]
+            self._layer_begin(l, +1)
             o.layernorm_fwd(self.x[l], P[pre + "ln_1.weight"], P[pre + "ln_1.bias"], self.ln1[l], st[0], st[1])
             w, g = self._w(pre + "attn.in_proj_weight")
             o.linear_fwd(self.ln1[l], w, self.qkv[l], bias=P[pre + "attn.in_proj_bias"], gather=g)
@@ -342,6 +411,7 @@ class NativeEngine:
             st = self.stats[l]
             # every buffer the side stream read for block l+1 is about to be overwritten
             self._join_side()
+            self._layer_begin(l, -1)
             # ---- MLP ----
             dy = self.dres
             if p > 0:
@@ -411,6 +481,13 @@ class NativeEngine:
         if self.dropout > 0:
             self.ops.step_seed_advance()      # new dropout masks every micro-step, also under graph replay
         self._gseq = 0
+        self._regather_tables = first_micro or not getattr(self, "keep_gathered", False)
+        if self._regather_tables:
+            self._invalidate_staging()      # weights moved at the optimizer boundary / slots were recycled
+        else:
+            # every block was gathered earlier in this accumulation cycle and nothing has updated the weights
+            # since.  Set explicitly (not inherited) so that a captured graph never depends on host-side history.
+            self._slot_layer, self._slot_pending = list(range(self.L)), [False] * self.L
         self._forward()
         self._loss_and_backward(first_micro, last_micro)
 
@@ -549,10 +626,13 @@ class NativeEngine:
 
         def fwd():
             self._gseq = 0
+            self._regather_tables = True
+            self._invalidate_staging()
             self._forward()
 
         def bwd():
             self._gseq = 4 * self.L if self.sharded_params else 0
+            self._invalidate_staging()
             self._loss_and_backward(True, True)
 
         if self.opt_in_backward:

@@ -50,9 +50,14 @@ def run_reference(a: argparse.Namespace) -> None:
         if rank == 0:
             emit({"impl": "reference", "unavailable": "baseline/_ref missing: run baseline/install_reference.sh"})
         return
+    if a.strategy in ("zero2", "zero3"):
+        if rank == 0:
+            emit({"impl": "reference", "unavailable": f"reference --strategy {a.strategy} needs DeepSpeed, which is not "
+                  "installed in this image and cannot be (no package index)"})
+        return
     port = env_int("MASTER_PORT", 29500) + 1 + (os.getpid() % 1 if ws == 1 else 0)
     outdir = tempfile.mkdtemp(prefix="refbench_")
-    cmd = [sys.executable, "-u", harness, "--strategy", "ddp", "--world-size", str(ws), "--rank", str(rank),
+    cmd = [sys.executable, "-u", harness, "--strategy", a.strategy, "--world-size", str(ws), "--rank", str(rank),
            "--local-rank", str(local_rank), "--master-addr", "127.0.0.1", "--master-port", str(port),
            "--tier", TIER, "--seq-len", str(SEQ), "--synthetic", "--steps", str(a.steps + a.warmup),
            "--warmup-steps", str(a.warmup), "--per-device-batch", str(BATCH), "--grad-accum", str(GRAD_ACCUM),
@@ -90,7 +95,7 @@ def run_reference(a: argparse.Namespace) -> None:
         "higher_is_better": True, "scaling": "weak", "vs_baseline": (tps / PUBLISHED_DDP[ws]) if ws in PUBLISHED_DDP else None,
         "dtype": "fp16 autocast over fp32 weights (reference default, TH:334-376)", "data": "synthetic",
         "config": {"model": "TinyGPT tier A (236.4M)", "global_batch": BATCH * ws, "seq_len": SEQ,
-                   "parallelism": f"dp{ws}", "strategy": "ddp", "grad_accum_flag": GRAD_ACCUM,
+                   "parallelism": f"dp{ws}", "strategy": a.strategy, "grad_accum_flag": GRAD_ACCUM,
                    "timer": "reference host perf_counter, rank 0 (TH:361-385)"},
         "e2e": {"value": tps, "unit": "tokens/s", "h2d_bytes_per_step": BATCH * SEQ * 8, "d2h_bytes_per_step": 4,
                 "note": "the reference loop itself copies int64 tokens from pinned memory and reads loss.item() every step"},

@@ -120,18 +120,23 @@ def main():
     from b200bench.config import StrategyConfig, get_model_config, load_deepspeed_config
     from b200bench.engine import NativeEngine
 
-    for strat in ("ddp", "zero2", "fsdp", "zero3"):
+    # fsdp / zero3 are checked with both weight all-gather schedules (inside the GEMM, and per block on the
+    # comm stream); each fused run is compared with the NCCL schedule of the same strategy
+    # the last case accumulates over 2 micro-steps: the second one reuses the blocks gathered by the first
+    for strat, pg, accum in (("ddp", None, 1), ("zero2", None, 1), ("fsdp", "stream", 1), ("fsdp", "gemm", 1),
+                             ("zero3", "stream", 1), ("zero3", "gemm", 1), ("zero3", "stream", 2)):
         cfgm = get_model_config("T", 128)
         sds = []
         for mode in ("fused", "nccl"):
             if strat in ("zero2", "zero3"):
-                sc = load_deepspeed_config(os.path.join(ROOT, f"configs/deepspeed/{strat}.json"), 2, 1, ws)
+                sc = load_deepspeed_config(os.path.join(ROOT, f"configs/deepspeed/{strat}.json"), 2, accum, ws)
             else:
                 sc = StrategyConfig()
+                sc.fsdp_reshard_after_forward = True      # two staging slots: blocks are gathered again in backward
             eng = NativeEngine(cfgm, strat, sc, ctx, dev, dropout=0.0, batch=2, seq_len=128, comm=mode,
-                               use_graph=(mode == "fused"))
+                               use_graph=(mode == "fused"), param_gather=pg, grad_accum=accum)
             g = torch.Generator(device=dev); g.manual_seed(5 + rank)
-            for _ in range(5):
+            for _ in range(5 * accum + (accum - 1) * 3):
                 tok = torch.randint(0, 512, (2, 128), device=dev, dtype=torch.int32, generator=g)
                 loss = eng.train_step(tok, tok)
             torch.cuda.synchronize(dev)
@@ -141,7 +146,7 @@ def main():
         # replicas must agree across ranks as well
         w = sds[0][0]["transformer.h.0.mlp.0.weight"].clone()
         w2 = w.clone(); dist.broadcast(w2, 0)
-        report(f"engine {strat}: fused == nccl", worst < 5e-3 and torch.equal(w, w2),
+        report(f"engine {strat}{'/' + pg if pg else ''}{' accum ' + str(accum) if accum > 1 else ''}: fused == nccl", worst < 5e-3 and torch.equal(w, w2),
                f"max_param_diff={worst:.2e} loss={sds[0][1]:.4f}/{sds[1][1]:.4f}")
 
     # ---- bandwidth / latency probes -----------------------------------------------------------------
