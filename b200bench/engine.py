@@ -16,10 +16,12 @@ ddp     full replica; K13 all-reduce(+1/N scale) per transformer block on a side
 zero2   weights replicated, gradients + optimizer state partitioned; K15 = pull-reduce of the
         partition + global-norm clip + AdamW + bf16 weight push to every peer, one kernel
                                                             [configs/deepspeed/zero2.json:10-44]
-fsdp /  weights, gradients and optimizer state partitioned (matrix region of the layout); K14: each
-zero3   weight matrix is gathered from the owners' shards INSIDE the GEMM that consumes it (forward
-        and again in dgrad), K15 updates the local shard; the vector tail (biases, LayerNorm) stays
-        replicated like DeepSpeed's persistence threshold        [TH:231-237, zero3.json:10-27]
+fsdp /  weights, gradients and optimizer state partitioned (matrix region of the layout).  Weight
+zero3   all-gather, param_gather="stream" (default): one peer-gather kernel per transformer block on the
+        comm stream, one block ahead of the compute stream; "gemm" (K14): each matrix is gathered from the
+        owners' shards INSIDE the GEMM that consumes it (forward and again in dgrad).  K15 updates the local
+        shard; the vector tail (biases, LayerNorm) stays replicated like DeepSpeed's persistence threshold
+                                                                 [TH:231-237, zero3.json:10-27]
 """
 from __future__ import annotations
 
