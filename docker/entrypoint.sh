@@ -11,7 +11,7 @@ echo "=== b200bench entrypoint: $(date -u +%FT%TZ) ==="
 
 : "${STRATEGY:=ddp}" "${WORLD_SIZE:=1}" "${LOCAL_RANK:=0}" "${MASTER_PORT:=29500}" "${SEQ_LEN:=2048}"
 : "${TIER:=A}" "${STEPS:=50}" "${WARMUP_STEPS:=5}" "${PER_DEVICE_BATCH:=1}" "${GRAD_ACCUM:=1}"
-: "${SYNTHETIC:=true}" "${RESULTS_DIR:=/results}" "${EXTRA_ARGS:=}"
+: "${SYNTHETIC:=true}" "${RESULTS_DIR:=/results}" "${EXTRA_ARGS:=}" "${APP_DIR:=/app}"
 VISIBLE_GPUS=$(nvidia-smi -L 2>/dev/null | wc -l || echo 0)
 : "${GPUS_PER_POD:=$VISIBLE_GPUS}"
 
@@ -32,11 +32,11 @@ COMMON=(--strategy "$STRATEGY" --seq-len "$SEQ_LEN" --tier "$TIER" --steps "$STE
         --results-dir "$RESULTS_DIR")
 [ "$SYNTHETIC" = "true" ] && COMMON+=(--synthetic)
 case "$STRATEGY" in
-  zero2|zero3) COMMON+=(--deepspeed-config "/app/configs/deepspeed/${STRATEGY}.json") ;;
-  fsdp)        COMMON+=(--fsdp-config /app/configs/fsdp/fsdp_config.yaml) ;;
+  zero2|zero3) COMMON+=(--deepspeed-config "$APP_DIR/configs/deepspeed/${STRATEGY}.json") ;;
+  fsdp)        COMMON+=(--fsdp-config "$APP_DIR/configs/fsdp/fsdp_config.yaml") ;;
 esac
 
-cd /app
+cd "$APP_DIR"
 if [ "$GPUS_PER_POD" -ge 2 ] && [ "$WORLD_SIZE" = "$GPUS_PER_POD" ]; then
   echo "=== single-host launch: $WORLD_SIZE ranks in this pod ==="
   # shellcheck disable=SC2086
@@ -44,5 +44,5 @@ if [ "$GPUS_PER_POD" -ge 2 ] && [ "$WORLD_SIZE" = "$GPUS_PER_POD" ]; then
 fi
 echo "=== rank-per-pod launch ==="
 # shellcheck disable=SC2086
-exec python -u /app/benchmarking/train_harness.py --world-size "$WORLD_SIZE" --rank "$RANK" \
+exec python -u "$APP_DIR/benchmarking/train_harness.py" --world-size "$WORLD_SIZE" --rank "$RANK" \
   --local-rank "$LOCAL_RANK" --master-addr "$MASTER_ADDR" --master-port "$MASTER_PORT" "${COMMON[@]}" $EXTRA_ARGS

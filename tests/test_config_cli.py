@@ -1,0 +1,100 @@
+"""Config loaders and CLI surface: CPU only."""
+import json
+import os
+
+import pytest
+
+from b200bench import cli
+from b200bench.config import StrategyConfig, get_model_config, load_deepspeed_config, load_fsdp_config
+from b200bench.parallel.torch_engine import effective_grad_accum
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REQUIRED = ["--strategy", "ddp", "--world-size", "1", "--rank", "0", "--tier", "A", "--seq-len", "2048",
+            "--steps", "10", "--per-device-batch", "1", "--grad-accum", "4", "--results-dir", "/tmp/r"]
+
+
+def test_tier_table_matches_reference():
+    # TH:157-179: A = 32000/1024/16/16, B = 32000/2048/32/32, block_size = seq_len
+    a, b = get_model_config("A", 2048), get_model_config("B", 4096)
+    assert (a["vocab_size"], a["n_embd"], a["n_head"], a["n_layer"], a["block_size"]) == (32000, 1024, 16, 16, 2048)
+    assert (b["vocab_size"], b["n_embd"], b["n_head"], b["n_layer"], b["block_size"]) == (32000, 2048, 32, 32, 4096)
+    with pytest.raises((ValueError, KeyError)):
+        get_model_config("Z", 128)
+
+
+@pytest.mark.parametrize("stage", ["zero2", "zero3"])
+def test_deepspeed_json_batch_keys_and_optimizer(stage):
+    path = os.path.join(ROOT, "configs", "deepspeed", f"{stage}.json")
+    raw = json.load(open(path))
+    cfg = load_deepspeed_config(path, micro_batch=3, grad_accum=4, world_size=8)
+    # the three batch keys are replaced by integers computed from the CLI (TH:251-262)
+    assert cfg.raw["train_micro_batch_size_per_gpu"] == 3
+    assert cfg.raw["gradient_accumulation_steps"] == 4
+    assert cfg.raw["train_batch_size"] == 3 * 4 * 8
+    assert all(isinstance(cfg.raw[k], int) for k in ("train_batch_size", "train_micro_batch_size_per_gpu",
+                                                     "gradient_accumulation_steps"))
+    opt = raw["optimizer"]["params"]
+    assert cfg.optim.weight_decay == pytest.approx(float(opt["weight_decay"]))
+    assert cfg.optim.grad_clip == pytest.approx(float(raw["gradient_clipping"]))
+    assert cfg.optim.warmup_steps == int(raw["scheduler"]["params"]["warmup_num_steps"])
+    assert cfg.optim.lr == pytest.approx(float(raw["scheduler"]["params"]["warmup_max_lr"]))
+    assert cfg.reduce_bucket_size == int(float(raw["zero_optimization"]["reduce_bucket_size"]))
+    if stage == "zero3":
+        assert cfg.stage3_max_live_parameters == int(float(raw["zero_optimization"]["stage3_max_live_parameters"]))
+
+
+def test_deepspeed_offload_is_rejected(tmp_path):
+    raw = json.load(open(os.path.join(ROOT, "configs", "deepspeed", "zero3.json")))
+    raw["zero_optimization"]["offload_param"] = {"device": "cpu"}
+    p = tmp_path / "z.json"
+    p.write_text(json.dumps(raw))
+    with pytest.raises(ValueError, match="offload"):
+        load_deepspeed_config(str(p), 1, 1, 2)
+
+
+def test_fsdp_yaml_is_applied(tmp_path):
+    cfg = load_fsdp_config(os.path.join(ROOT, "configs", "fsdp", "fsdp_config.yaml"))
+    assert cfg.fsdp_sharding_strategy == "full_shard"
+    assert cfg.fsdp_auto_wrap_policy == "transformer_block"
+    assert cfg.fsdp_forward_prefetch is True
+    assert cfg.fsdp_reshard_after_forward == "auto"
+    p = tmp_path / "f.yaml"
+    p.write_text("fsdp_config:\n  reshard_after_forward: true\n  forward_prefetch: false\n")
+    cfg = load_fsdp_config(str(p))
+    assert cfg.fsdp_reshard_after_forward is True and cfg.fsdp_forward_prefetch is False
+    p.write_text("fsdp_config:\n  reshard_after_forward: sometimes\n")
+    with pytest.raises(ValueError, match="reshard_after_forward"):
+        load_fsdp_config(str(p))
+    p.write_text("fsdp_config:\n  cpu_offload: true\n")
+    with pytest.raises(ValueError, match="cpu_offload"):
+        load_fsdp_config(str(p))
+    assert isinstance(load_fsdp_config(""), StrategyConfig)      # no file: defaults
+
+
+def test_grad_accum_semantics():
+    # only the ZeRO strategies honour --grad-accum in reference mode
+    assert effective_grad_accum("ddp", 4, "reference") == 1
+    assert effective_grad_accum("fsdp", 4, "reference") == 1
+    assert effective_grad_accum("zero2", 4, "reference") == 4
+    assert effective_grad_accum("zero3", 4, "reference") == 4
+    assert effective_grad_accum("ddp", 4, "uniform") == 4
+
+
+def test_cli_reference_flags_and_defaults():
+    a = cli.parse_args(REQUIRED + ["--synthetic", "--fsdp-config", "x.yaml"])
+    # defaults of the reference parser (TH:465-498)
+    assert (a.local_rank, a.master_addr, a.master_port, a.warmup_steps) == (0, "localhost", 29500, 5)
+    assert a.synthetic and a.fsdp_config == "x.yaml" and a.deepspeed_config is None
+    # extensions keep reference behaviour by default
+    assert (a.attn, a.dropout, a.grad_accum_mode, a.timer, a.comm) == ("bidir", 0.1, "reference", "device", "fused")
+
+
+def test_cli_rejects_zero_without_config_and_unknown_strategy():
+    argv = [x if x != "ddp" else "zero2" for x in REQUIRED]
+    with pytest.raises(ValueError, match="deepspeed-config"):          # TH:501-502
+        cli.parse_args(argv)
+    assert cli.parse_args(argv + ["--deepspeed-config", "c.json"]).deepspeed_config == "c.json"
+    with pytest.raises(SystemExit):
+        cli.parse_args([x if x != "ddp" else "pipeline" for x in REQUIRED])
+    with pytest.raises(SystemExit):                                    # a required flag is missing
+        cli.parse_args(REQUIRED[:-2])
