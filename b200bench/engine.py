@@ -246,7 +246,10 @@ class NativeEngine:
                 (self.L * (a1 - a0) * 2 <= 0.05 * torch.cuda.get_device_properties(dev).total_memory)
         self.keep_gathered = bool(keep) and self.param_gather == "stream"
         self.n_slots = self.L if self.keep_gathered else 2
-        self.gather_ctas = int(os.environ.get("B200BENCH_GATHER_CTAS", "32"))
+        # CTAs of one block gather: 32 are enough for tier A's 25 MB blocks (measured, profiles/README.md); big
+        # blocks (403 MB at the 7B shape) need the full ~650 GB/s of a 128-CTA copy to stay ahead of the compute
+        self.gather_ctas = int(os.environ.get("B200BENCH_GATHER_CTAS", "0")) or \
+            min(128, max(32, (a1 - a0) * 2 // (2 << 20)))
         self.stage_layer = (torch.empty(self.n_slots, a1 - a0, dtype=BF16, device=dev)
                             if self.param_gather == "stream" else None)
         self._invalidate_staging()

@@ -416,21 +416,26 @@ peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t 
 __global__ void __launch_bounds__(COMM_THREADS, 2)
 gather_range_kernel(PeerPtrs src, __nv_bfloat16* __restrict__ dst, unsigned long long flat_off,
                     unsigned long long n, unsigned long long shard) {
+  constexpr int U = 8;   // 16-byte loads in flight per thread (NVLink round trip ~2.5 us)
   const size_t nvec = n >> 3;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
-  for (size_t i0 = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += 4 * stride) {
-    uint4 v[4];
+  // owner = flat / shard, in units of 8 elements so that it is a 32-bit division (flat_off, n and shard
+  // are multiples of 8; the host rejects ranges whose vector index does not fit 32 bits)
+  const uint32_t vec0 = static_cast<uint32_t>(flat_off >> 3);
+  const uint32_t shard_vec = static_cast<uint32_t>(shard >> 3);
+  for (size_t i0 = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += U * stride) {
+    uint4 v[U];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const size_t i = i0 + u * stride;
       if (i < nvec) {
-        const size_t flat = flat_off + i * 8;
-        const int owner = static_cast<int>(flat / shard);
-        v[u] = ld_peer_v4(static_cast<const __nv_bfloat16*>(src.p[owner]) + flat);
+        const uint32_t fv = vec0 + static_cast<uint32_t>(i);
+        const int owner = static_cast<int>(fv / shard_vec);
+        v[u] = ld_peer_v4(static_cast<const __nv_bfloat16*>(src.p[owner]) + static_cast<size_t>(fv) * 8);
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const size_t i = i0 + u * stride;
       if (i < nvec) reinterpret_cast<uint4*>(dst)[i] = v[u];
     }
@@ -535,6 +540,7 @@ extern "C" int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst,
                                       unsigned long long flat_off, unsigned long long n,
                                       unsigned long long shard_elems, int ctas, void* stream) {
   if (n % 8 || flat_off % 8 || shard_elems % 8 || ws > MAX_RANKS) return -2;
+  if (((flat_off + n) >> 3) > 0xFFFFFFFFull || (shard_elems >> 3) > 0xFFFFFFFFull || shard_elems == 0) return -3;
   gather_range_kernel<<<ctas > 0 ? ctas : 128, COMM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       make_ptrs(shard_adj, ws), static_cast<__nv_bfloat16*>(dst), flat_off, n, shard_elems);
   return static_cast<int>(cudaGetLastError());
