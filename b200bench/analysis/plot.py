@@ -10,7 +10,7 @@ from __future__ import annotations
 import argparse
 import math
 from pathlib import Path
-from typing import Callable, Dict, List, Optional, Sequence, Tuple
+from typing import Callable, Dict, List, Optional, Tuple
 
 import pandas as pd
 

@@ -11,9 +11,7 @@ autocast + GradScaler, identical initial weights on every rank.
 """
 from __future__ import annotations
 
-import os
-import time
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict
 
 import torch
 

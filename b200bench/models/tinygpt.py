@@ -13,7 +13,6 @@ still called ``in_proj_weight`` with Q|K|V row order), and attention never mater
 """
 from __future__ import annotations
 
-import math
 from typing import Optional, Tuple
 
 import torch

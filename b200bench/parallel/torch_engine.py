@@ -14,7 +14,6 @@ zero3  zero2 + parameters partitioned: all-gather before forward              ze
 """
 from __future__ import annotations
 
-import math
 from typing import Dict, Optional
 
 import torch

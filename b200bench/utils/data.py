@@ -10,8 +10,6 @@ Targets equal inputs, unshifted, as in ``TH:359`` unless ``shift_tar
 """
 from __future__ import annotations
 
-from typing import Iterator, Optional, Tuple
-
 import torch
 
 

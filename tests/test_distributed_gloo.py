@@ -1,9 +1,7 @@
 """CPU/gloo world_size=2 plumbing (first BASELINE.json config) and strategy equivalence."""
 import json
 import os
-import sys
 
-import pytest
 import torch
 
 from b200bench.launch import launch

@@ -1,7 +1,6 @@
 """Result schema, metric formulas, marker round-trip, efficiency formula vs the published rows."""
 import argparse
 import json
-import re
 import subprocess
 
 import pandas as pd
