@@ -26,6 +26,14 @@ build/bin/%: csrc/tests/%.cu $(OBJS) $(wildcard csrc/tests/*.cu)
 ptxas-info:
 	@for f in $(SRCS); do echo "== $$f"; $(NVCC) $(NVCCFLAGS) -Xptxas -v -c $$f -o /dev/null 2>&1 | grep -E "registers|spill" ; done
 
+# Debug build of the collectives: a timed-out flag wait prints rank / CTA / flag plane / expected and
+# last seen value before it traps.  Separate library, the default build is unchanged:
+#   make debug-comm && B200BENCH_LIB=b200bench/lib/libb200bench_debug.so python ...
+debug-comm: $(OBJS)
+	@mkdir -p build/obj_debug b200bench/lib
+	$(NVCC) $(NVCCFLAGS) -DB200_COMM_DEBUG -c csrc/comm.cu -o build/obj_debug/comm.o
+	$(NVCC) $(ARCH) -shared -o b200bench/lib/libb200bench_debug.so build/obj_debug/comm.o $(filter-out build/obj/comm.o,$(OBJS)) -lcudart
+
 # compute-sanitizer targets (need a GPU): every single-GPU kernel at small shapes, see csrc/tests/test_sanitize.cu
 SANITIZER ?= compute-sanitizer
 memcheck: build/bin/test_sanitize
@@ -38,4 +46,4 @@ initcheck: build/bin/test_sanitize
 clean:
 	rm -rf build b200bench/lib
 
-.PHONY: all clean ptxas-info memcheck synccheck initcheck
+.PHONY: all clean ptxas-info memcheck synccheck initcheck debug-comm

@@ -16,7 +16,8 @@ from typing import Optional
 import torch
 
 _ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-LIB_PATH = os.path.join(_ROOT, "b200bench", "lib", "libb200bench.so")
+# B200BENCH_LIB selects another build of the same ABI (e.g. `make debug-comm` -> libb200bench_debug.so)
+LIB_PATH = os.environ.get("B200BENCH_LIB") or os.path.join(_ROOT, "b200bench", "lib", "libb200bench.so")
 
 EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_RESID, EPI_DGELU, EPI_ACCUM = range(6)
 

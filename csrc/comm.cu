@@ -19,6 +19,7 @@
 // (st.release.sys / ld.acquire.sys) with an epoch counter kept in device memory, so the kernels
 // can be replayed from a CUDA graph.  All spin loops are bounded and trap instead of hanging.
 #include <cuda_bf16.h>
+#include <cstdio>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
@@ -84,7 +85,13 @@ __device__ __forceinline__ void rank_barrier(const PeerPtrs& flags, int rank, in
                           (kind * COMM_MAX_CTAS + blockIdx.x) * MAX_RANKS + peer;
     uint32_t spins = 0;
     while (static_cast<int32_t>(ld_acquire_sys(src) - value) < 0) {
-      if (++spins > (1u << 28)) __trap();  // a peer never arrived: abort instead of hanging
+      if (++spins > (1u << 28)) {  // a peer never arrived: abort instead of hanging
+#ifdef B200_COMM_DEBUG
+        printf("[b200 comm] rank %d CTA %d: rank %d never reached flag plane %d value %u (last seen %u)\n", rank,
+               static_cast<int>(blockIdx.x), peer, kind, value, ld_acquire_sys(src));
+#endif
+        __trap();
+      }
     }
   }
   __syncthreads();
@@ -98,7 +105,13 @@ __device__ __forceinline__ void grid_barrier(uint32_t* ctr, uint32_t target) {
     atomicAdd(ctr, 1u);
     uint32_t spins = 0;
     while (static_cast<int32_t>(ld_acquire_gpu(ctr) - target) < 0) {
-      if (++spins > (1u << 28)) __trap();
+      if (++spins > (1u << 28)) {
+#ifdef B200_COMM_DEBUG
+        printf("[b200 comm] CTA %d: grid barrier stuck at %u of %u\n", static_cast<int>(blockIdx.x),
+               ld_acquire_gpu(ctr), target);
+#endif
+        __trap();
+      }
     }
   }
   __syncthreads();
