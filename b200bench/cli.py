@@ -57,6 +57,9 @@ def build_parser() -> argparse.ArgumentParser:
     x.add_argument("--save-state-dict", type=str, default=None)
     x.add_argument("--load-state-dict", type=str, default=None)
     x.add_argument("--profile", action="store_true", help="add a per-phase time breakdown to the result")
+    x.add_argument("--nvtx", action="store_true",
+                   help="NVTX range per training step (and per phase when the engine runs eagerly) for nsys / ncu")
+    x.add_argument("--no-graph", action="store_true", help="run the native engine eagerly instead of CUDA-graph replay")
     return p
 
 

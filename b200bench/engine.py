@@ -55,8 +55,9 @@ class NativeEngine:
     def __init__(self, model_cfg: Dict[str, int], strategy: str, cfg: StrategyConfig, ctx: DistCtx,
                  device: torch.device, grad_accum: int = 1, dropout: float = 0.1, causal: bool = False,
                  batch: int = 1, seq_len: int = 2048, comm: str = "fused", use_graph: bool = True,
-                 seed: int = 42, param_gather: Optional[str] = None):
+                 seed: int = 42, param_gather: Optional[str] = None, nvtx: bool = False):
         self.ops = _ops.load()
+        self.nvtx = bool(nvtx)                # host-side ranges: meaningful for eager steps and graph capture only
         # fsdp / zero3 weight all-gather: "gemm" = gather warps inside the consuming GEMM (K14), "stream" = one
         # peer-gather kernel per transformer block on the comm stream, one block ahead of the compute stream
         self.param_gather = param_gather or os.environ.get("B200BENCH_PARAM_GATHER", "stream")
@@ -493,8 +494,15 @@ class NativeEngine:
             # every block was gathered earlier in this accumulation cycle and nothing has updated the weights
             # since.  Set explicitly (not inherited) so that a captured graph never depends on host-side history.
             self._slot_layer, self._slot_pending = list(range(self.L)), [False] * self.L
+        if self.nvtx:
+            torch.cuda.nvtx.range_push("forward")
         self._forward()
+        if self.nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("loss+backward" + ("+reduce" if last_micro else ""))
         self._loss_and_backward(first_micro, last_micro)
+        if self.nvtx:
+            torch.cuda.nvtx.range_pop()
 
     def _run_micro(self, first_micro: bool, last_micro: bool) -> None:
         if not self.use_graph:

@@ -65,7 +65,8 @@ def build_engine(args: Any, model_cfg: Dict[str, int], cfg: StrategyConfig, ctx:
 
         return NativeEngine(model_cfg, args.strategy, cfg, ctx, device, grad_accum=args.grad_accum,
                             dropout=dropout, causal=causal, batch=args.per_device_batch,
-                            seq_len=args.seq_len, comm=getattr(args, "comm", "fused"))
+                            seq_len=args.seq_len, comm=getattr(args, "comm", "fused"),
+                            use_graph=not getattr(args, "no_graph", False), nvtx=getattr(args, "nvtx", False))
     from .parallel.torch_engine import TorchEngine
 
     native_ops = None
@@ -116,8 +117,11 @@ def train(args: Any) -> Dict[str, Any]:
     loss_slots = torch.zeros(max(1, args.steps), dtype=torch.float32,
                              pin_memory=(device.type == "cuda"))
     profile = getattr(args, "profile", False)
+    nvtx = bool(getattr(args, "nvtx", False)) and device.type == "cuda"
 
     for step in range(args.steps):
+        if nvtx:
+            torch.cuda.nvtx.range_push(f"step {step}" + (" (warm-up)" if step < args.warmup_steps else ""))
         timer.start()
         tokens = source.next()                                          # H2D from pinned memory
         if shift:
@@ -127,6 +131,8 @@ def train(args: Any) -> Dict[str, Any]:
         loss = engine.train_step(tokens, targets)
         loss_slots[step].copy_(loss.detach().float().reshape(()), non_blocking=True)   # D2H of the step result
         dt = timer.stop(keep=step >= args.warmup_steps)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         if is_main and log_every > 0 and step % log_every == 0:
             if device.type == "cuda":
                 torch.cuda.current_stream().synchronize()
