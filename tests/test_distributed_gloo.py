@@ -16,9 +16,12 @@ COMMON = ["--tier", "T", "--seq-len", "32", "--warmup-steps", "1", "--per-device
 def _run(tmp_path, strategy, nproc, steps=4, extra=()):
     out = tmp_path / f"{strategy}_{nproc}"
     sd = out / "sd.pt"
-    rc = launch(nproc, ["--strategy", strategy, "--steps", str(steps), "--grad-accum", "1",
-                        "--results-dir", str(out), "--save-state-dict", str(sd)] + COMMON + list(extra),
-                timeout=240, env_extra={"PYTHONPATH": ROOT})
+    for attempt in range(2):      # one retry: the rendezvous port is picked by bind-and-release, which can race
+        rc = launch(nproc, ["--strategy", strategy, "--steps", str(steps), "--grad-accum", "1",
+                            "--results-dir", str(out), "--save-state-dict", str(sd)] + COMMON + list(extra),
+                    timeout=240, env_extra={"PYTHONPATH": ROOT})
+        if rc == 0:
+            break
     assert rc == 0
     res = json.load(open(out / f"result_{strategy}_ws{nproc}_seq32_tierT.json"))
     return res, torch.load(sd)
