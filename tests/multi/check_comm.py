@@ -170,6 +170,34 @@ def main():
                 if rank == 0:
                     print(f"[bench] allreduce {mb:4d} MiB ctas={ctas:3d}: fused {ms*1e3:8.1f} us (busbw {bus:6.0f} GB/s)   "
                           f"nccl {ms_n*1e3:8.1f} us", flush=True)
+        # K15 on a tier-A-sized buffer (236.4 M elements): reduce-scatter + AdamW (+ push to every peer)
+        nk = 236_400_000 // (8 * ws) * (8 * ws)
+        gk = comm.alloc("gk", nk, torch.bfloat16)
+        wk = comm.alloc("wk", nk, torch.bfloat16)
+        shard = nk // ws
+        master = torch.zeros(shard, device=dev); m1 = torch.zeros(shard, device=dev); m2 = torch.zeros(shard, device=dev)
+        gsh = torch.zeros(shard, dtype=torch.bfloat16, device=dev)
+        hp = torch.zeros(16, device=dev)
+        ops.adamw_set_hp(hp, 1e-4, 0.9, 0.999, 1e-8, 0.01, 10.0, 31.6, 1.0 / ws, 0.0)
+        for push in (True, False):
+            ms = timed(lambda: comm.rs_adamw(gk, wk, rank * shard, shard, master, m1, m2, gsh, hp, push_all=push),
+                       5, ws, dev)
+            nvl = (ws - 1) * shard * 2 * (2 if push else 1)        # bytes pulled (+ pushed) over NVLink per GPU
+            hbm = shard * 28 + ws * shard * 2                       # optimizer traffic + local reads of the ws slices
+            if rank == 0:
+                print(f"[bench] K15 rs_adamw push_all={int(push)} {nk/1e6:.1f} M elements: {ms*1e3:7.1f} us  "
+                      f"NVLink {nvl/ms/1e6:5.0f} GB/s per direction-equivalent, roofline max(NVLink {nvl/770e9*1e6:.0f} us, "
+                      f"HBM {hbm/6454.6e9*1e6:.0f} us)", flush=True)
+        # block gather (the fsdp / zero3 weight all-gather): 25 MB = one tier-A block, 403 MB = one 7B-shaped block
+        table = comm.adjusted_table(wk, shard)
+        for mb in (25, 403):
+            cnt = min(mb * 1000 * 1000 // 2 // 8 * 8, nk)
+            dstg = torch.empty(cnt, dtype=torch.bfloat16, device=dev)
+            for ctas in (32, 64, 128):
+                ms = timed(lambda: comm.gather_range(table, dstg, 0, cnt, shard, ctas=ctas), 10, ws, dev)
+                if rank == 0:
+                    print(f"[bench] gather_range {cnt*2/1e6:6.1f} MB ctas={ctas:3d}: {ms*1e3:7.1f} us  "
+                          f"{cnt*2/ms/1e6:5.0f} GB/s", flush=True)
     comm.close()
     dist.barrier()
     if rank == 0:
