@@ -165,6 +165,17 @@ def train(args: Any) -> Dict[str, Any]:
         "attn": getattr(args, "attn", "bidir"),
         "gpu_launches_per_step": engine.kernel_launches_per_step(),
     }
+    try:                                  # closed-form work of one micro-step vs the measured peaks (analysis/roofline.py)
+        from .analysis.roofline import roofline
+
+        rf = roofline(model_cfg, args.strategy, args.world_size, args.per_device_batch, args.seq_len,
+                      extra["grad_accum_effective"], bool(getattr(engine, "keep_gathered", True)),
+                      metrics["mean_step_time_sec"] * 1e3 if metrics["mean_step_time_sec"] > 0 else None)
+        extra["model_tflops_per_gpu"] = rf.get("model_tflops_achieved")
+        extra["step_roofline_ms"] = rf["roofline_ms"]
+        extra["fraction_of_step_roofline"] = rf.get("fraction_of_roofline")
+    except Exception as e:  # never let the accounting break a benchmark run
+        extra["roofline_error"] = repr(e)
     if profile and hasattr(engine, "profile_breakdown"):
         extra["profile"] = engine.profile_breakdown()
     result = make_result(args, metrics, extra)
