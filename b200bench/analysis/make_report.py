@@ -28,9 +28,9 @@ TRADEOFFS = {
     ],
     "FSDP (Fully Sharded Data Parallel)": [
         "Parameters, gradients and optimizer state partitioned per transformer block",
-        "Parameter all-gather is fused into the consuming QKV/MLP GEMMs; gradient reduce-scatter is fused with the AdamW update",
-        "NVLink traffic per step: 3 x param_bytes x (N-1)/N per GPU",
-        "Memory: O(model_size / world_size) per GPU plus one block of gathered weights",
+        "Weights are gathered one transformer block ahead of the compute stream by a peer-memory kernel (or inside the consuming GEMMs, param_gather=gemm); gradient reduce-scatter is fused with the AdamW update",
+        "NVLink traffic per step: 2 x param_bytes x (N-1)/N per GPU (3 x when blocks are re-sharded after forward)",
+        "Memory: optimizer state and weights O(model_size / world_size) per GPU, plus the local gradient buffer and the gathered blocks (two, or all of them when they fit)",
     ],
     "ZeRO-2": [
         "Optimizer state and gradients partitioned, parameters replicated",
@@ -41,8 +41,8 @@ TRADEOFFS = {
     "ZeRO-3": [
         "Parameters, gradients AND optimizer state partitioned",
         "Same fused paths as FSDP, DeepSpeed-style configuration (clip 1.0, WarmupLR, --grad-accum honoured)",
-        "Maximum memory efficiency; parameter gathers are paid on every micro-step",
-        "Memory: O(model_size / world_size) per GPU",
+        "Gathered blocks are reused for the rest of an accumulation cycle when the model fits stage3_max_live_parameters; otherwise they are gathered again on every micro-step, forward and backward",
+        "Memory: as FSDP",
     ],
 }
 
@@ -96,6 +96,19 @@ def generate_report(csv_path: str, output_dir: str) -> Path:
         md.append(_table(rows, ["World Size", "Seq Len", "Tokens/sec", "Step Time (s)", "Peak VRAM (GB)",
                                 "H2D GB/s/GPU", "Scaling Eff (%)"]))
     md.append("---\n")
+
+    if "model_tflops_per_gpu" in df.columns and df["model_tflops_per_gpu"].notna().any():
+        md.append("## Hardware Efficiency\n")
+        md.append("Model FLOPs per GPU (6 x matmul parameters x tokens + attention) over the measured step time, and the "
+                  "step time a perfect overlap of compute, optimizer HBM traffic and NVLink traffic would take at the "
+                  "measured peaks (`python -m b200bench.analysis.roofline`).\n")
+        sub = df[df["model_tflops_per_gpu"].notna()]
+        rows = [[f"{r.strategy.upper():8s}", f"{int(r.world_size):9d}", f"{int(r.seq_len):7d}", f"{str(r.tier):4s}",
+                 f"{r.model_tflops_per_gpu:12.0f}", f"{r.step_roofline_ms:11.2f}", f"{1e3 * r.mean_step_time_sec:11.2f}",
+                 f"{r.fraction_of_step_roofline:8.2f}"] for r in sub.itertuples()]
+        md.append(_table(rows, ["Strategy", "World Size", "Seq Len", "Tier", "TFLOP/s per GPU", "Roofline (ms)",
+                                "Measured (ms)", "Fraction"]))
+        md.append("---\n")
 
     md.append("## Key Findings\n")
     b = df.loc[df["tokens_per_sec"].idxmax()]

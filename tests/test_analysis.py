@@ -55,3 +55,14 @@ def test_single_seq_len_skips_vram_plot(tmp_path):
     assert "vram_vs_seqlen.png" not in [p.name for p in made]
     rep = make_report.generate_report(str(csv), str(tmp_path / "s")).read_text()
     assert "vram_vs_seqlen.png" not in rep
+
+
+def test_hardware_efficiency_section_appears_with_roofline_columns(tmp_path):
+    res = tmp_path / "results"
+    _write(res, "a", world_size=1, model_tflops_per_gpu=428.0, step_roofline_ms=3.59, fraction_of_step_roofline=0.42,
+           mean_step_time_sec=0.00864)
+    _write(res, "b", world_size=8, tokens_per_sec=7000.0)                 # an older result without the columns
+    csv = parse_metrics.parse_results(str(res), str(tmp_path / "s"))
+    rep = make_report.generate_report(str(csv), str(tmp_path / "s")).read_text()
+    assert "## Hardware Efficiency" in rep and "428" in rep and "0.42" in rep
+    assert rep.index("## Hardware Efficiency") < rep.index("## Key Findings")
