@@ -71,6 +71,11 @@ class StrategyConfig:
     fsdp_sync_module_states: bool = True
     # "auto": keep the gathered blocks from forward to backward when they take < 5 % of device memory
     fsdp_reshard_after_forward: Any = "auto"
+    # engine knobs settable from the strategy files ("b200bench" section of the JSON / keys of the YAML);
+    # None / 0 = engine default.  Environment variables B200BENCH_* override them (engine.py).
+    param_gather: Optional[str] = None      # "stream" | "gemm": fsdp / zero3 weight all-gather schedule
+    gather_ctas: int = 0                    # CTAs of one block gather
+    comm_ctas: int = 0                      # CTAs of one K13 all-reduce
     # gradient accumulation: "reference" = only ZeRO strategies honour --grad-accum
     grad_accum_mode: str = "reference"
     raw: Dict[str, Any] = field(default_factory=dict)
@@ -81,6 +86,20 @@ class StrategyConfig:
 
 def _num(x: Any) -> int:
     return int(float(x))
+
+
+def _apply_engine_knobs(cfg: "StrategyConfig", section: Dict[str, Any]) -> None:
+    pg = section.get("param_gather")
+    if pg is not None:
+        if pg not in ("stream", "gemm"):
+            raise ValueError(f"param_gather must be 'stream' or 'gemm', got {pg!r}")
+        cfg.param_gather = pg
+    for key in ("gather_ctas", "comm_ctas"):
+        if section.get(key) is not None:
+            v = int(section[key])
+            if not 0 <= v <= 512:
+                raise ValueError(f"{key} must be between 0 (engine default) and 512, got {v}")
+            setattr(cfg, key, v)
 
 
 def load_deepspeed_config(path: str, micro_batch: int, grad_accum: int, world_size: int) -> StrategyConfig:
@@ -116,6 +135,7 @@ def load_deepspeed_config(path: str, micro_batch: int, grad_accum: int, world_si
     cfg.stage3_param_persistence_threshold = _num(
         z.get("stage3_param_persistence_threshold", cfg.stage3_param_persistence_threshold))
     cfg.stage3_max_live_parameters = _num(z.get("stage3_max_live_parameters", cfg.stage3_max_live_parameters))
+    _apply_engine_knobs(cfg, raw.get("b200bench", {}))
     for dev_key in ("offload_optimizer", "offload_param"):
         dev = z.get(dev_key, {}).get("device", "none")
         if dev not in ("none", None):
@@ -142,6 +162,7 @@ def load_fsdp_config(path: Optional[str]) -> StrategyConfig:
     if not (isinstance(r, bool) or r == "auto"):
         raise ValueError(f"reshard_after_forward must be true, false or auto, got {r!r}")
     cfg.fsdp_reshard_after_forward = r
+    _apply_engine_knobs(cfg, body)
     if body.get("cpu_offload", False):
         raise ValueError("cpu_offload is not supported (reference: CPUOffload(False), TH:234)")
     return cfg

@@ -60,7 +60,9 @@ class NativeEngine:
         self.nvtx = bool(nvtx)                # host-side ranges: meaningful for eager steps and graph capture only
         # fsdp / zero3 weight all-gather: "gemm" = gather warps inside the consuming GEMM (K14), "stream" = one
         # peer-gather kernel per transformer block on the comm stream, one block ahead of the compute stream
-        self.param_gather = param_gather or os.environ.get("B200BENCH_PARAM_GATHER", "stream")
+        # precedence: constructor argument, environment, strategy config file, default
+        self.param_gather = (param_gather or os.environ.get("B200BENCH_PARAM_GATHER")
+                             or getattr(cfg, "param_gather", None) or "stream")
         if self.param_gather not in ("gemm", "stream"):
             raise ValueError(f"param_gather must be 'gemm' or 'stream', got {self.param_gather!r}")
         self.n_slots = 2
@@ -92,7 +94,8 @@ class NativeEngine:
             # K13 CTA count: more peers per CTA means more loads in flight per CTA, so fewer CTAs (= fewer SMs
             # taken from the backward GEMMs) reach the same NVLink rate.  Measured: N=8 16 CTAs 9.34 ms/step,
             # 32: 9.41, 64: 9.60 (profiles/n8*); N=2 needs 64 (profiles/comm_n2_v2.log).
-            ctas = int(os.environ.get("B200BENCH_COMM_CTAS", "0")) or {2: 64, 4: 32}.get(ws, 16)
+            ctas = (int(os.environ.get("B200BENCH_COMM_CTAS", "0")) or int(getattr(cfg, "comm_ctas", 0) or 0)
+                    or {2: 64, 4: 32}.get(ws, 16))
             self.comm = PeerComm(ctx, device, comm_ctas=ctas)
         self.sharded_params = self.comm is not None and strategy in SHARDED_PARAMS
 
@@ -249,8 +252,9 @@ class NativeEngine:
         self.n_slots = self.L if self.keep_gathered else 2
         # CTAs of one block gather: 32 are enough for tier A's 25 MB blocks (measured, profiles/README.md); big
         # blocks (403 MB at the 7B shape) need the full ~650 GB/s of a 128-CTA copy to stay ahead of the compute
-        self.gather_ctas = int(os.environ.get("B200BENCH_GATHER_CTAS", "0")) or \
-            min(128, max(32, (a1 - a0) * 2 // (2 << 20)))
+        self.gather_ctas = (int(os.environ.get("B200BENCH_GATHER_CTAS", "0"))
+                            or int(getattr(self.cfg, "gather_ctas", 0) or 0)
+                            or min(128, max(32, (a1 - a0) * 2 // (2 << 20))))
         self.stage_layer = (torch.empty(self.n_slots, a1 - a0, dtype=BF16, device=dev)
                             if self.param_gather == "stream" else None)
         self._invalidate_staging()

@@ -98,3 +98,25 @@ def test_cli_rejects_zero_without_config_and_unknown_strategy():
         cli.parse_args([x if x != "ddp" else "pipeline" for x in REQUIRED])
     with pytest.raises(SystemExit):                                    # a required flag is missing
         cli.parse_args(REQUIRED[:-2])
+
+
+def test_engine_knobs_come_from_the_strategy_files(tmp_path):
+    z3 = load_deepspeed_config(os.path.join(ROOT, "configs", "deepspeed", "zero3.json"), 1, 4, 8)
+    assert z3.param_gather == "stream" and z3.gather_ctas == 0 and z3.comm_ctas == 0
+    raw = json.load(open(os.path.join(ROOT, "configs", "deepspeed", "zero3.json")))
+    raw["b200bench"].update({"param_gather": "gemm", "gather_ctas": 64, "comm_ctas": 16})
+    p = tmp_path / "z3.json"
+    p.write_text(json.dumps(raw))
+    cfg = load_deepspeed_config(str(p), 1, 4, 8)
+    assert (cfg.param_gather, cfg.gather_ctas, cfg.comm_ctas) == ("gemm", 64, 16)
+    raw["b200bench"]["param_gather"] = "ring"
+    p.write_text(json.dumps(raw))
+    with pytest.raises(ValueError, match="param_gather"):
+        load_deepspeed_config(str(p), 1, 4, 8)
+    raw["b200bench"].update({"param_gather": "stream", "gather_ctas": 100000})
+    p.write_text(json.dumps(raw))
+    with pytest.raises(ValueError, match="gather_ctas"):
+        load_deepspeed_config(str(p), 1, 4, 8)
+    f = load_fsdp_config(os.path.join(ROOT, "configs", "fsdp", "fsdp_config.yaml"))
+    assert f.param_gather == "stream" and f.gather_ctas == 0
+    assert StrategyConfig().param_gather is None                      # plain ddp: engine default
