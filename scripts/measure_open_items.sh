@@ -5,9 +5,10 @@
 #   scripts/measure_open_items.sh sharded 8    # fsdp + zero3 with the block-prefetch gather (~1 min on N GPUs)
 #   scripts/measure_open_items.sh tier7b 8     # Mistral-7B-shaped ZeRO-3                    (~1 min on N GPUs)
 #   scripts/measure_open_items.sh gather_ab 2  # param_gather stream vs gemm, same box       (~1.5 min on 2 GPUs)
+#   scripts/measure_open_items.sh library 1    # our GEMMs / attention vs cuBLAS / SDPA at the same shapes (~0.5 min)
 set -uo pipefail
 cd "$(dirname "${BASH_SOURCE[0]}")/.."
-STAGE="${1:?stage: comm | sharded | tier7b | gather_ab}"
+STAGE="${1:?stage: comm | sharded | tier7b | gather_ab | library}"
 N="${2:?number of GPUs}"
 OUT="${OUT:-gpurun_out/open_${STAGE}_n$N}"
 mkdir -p "$OUT"
@@ -30,5 +31,8 @@ case "$STAGE" in
     for g in stream gemm; do
       B200BENCH_PARAM_GATHER=$g STRATEGIES="fsdp zero3" REF=0 CHECK=0 DIAG=0 OUT="$OUT/$g" scripts/validate_multi.sh "$N"
     done ;;
+  library)
+    python scripts/compare_library_kernels.py > "$OUT/library_compare.md" 2> "$OUT/library_compare.err"
+    echo "exit code $?"; cat "$OUT/library_compare.md" ;;
   *) echo "unknown stage $STAGE" >&2; exit 1 ;;
 esac
