@@ -36,8 +36,28 @@ def env_int(name: str, default: int) -> int:
     return int(os.environ.get(name, default))
 
 
+_RESULT_FD = None      # the original stdout, once quiet_stdout() has pointed fd 1 at stderr
+
+
+def quiet_stdout() -> None:
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner with
+    printf), so for the duration of the run file descriptor 1 is pointed at stderr and the result line alone is
+    written to the saved original."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
 def emit(obj: dict) -> None:
-    print(json.dumps(obj), flush=True)
+    line = (json.dumps(obj) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, line)
 
 
 # ------------------------------------------------------------------------------------------
@@ -238,6 +258,7 @@ def main() -> None:
     ap.add_argument("--diag", action="store_true", help="after the timed arms, print a per-phase breakdown to stderr")
     ap.add_argument("--ref-timeout", type=float, default=180.0, help="seconds before the reference arm is abandoned")
     a = ap.parse_args()
+    quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
