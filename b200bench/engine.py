@@ -17,11 +17,12 @@ zero2   weights replicated, gradients + optimizer state partitioned; K15 = pull-
         partition + global-norm clip + AdamW + bf16 weight push to every peer, one kernel
                                                             [configs/deepspeed/zero2.json:10-44]
 fsdp /  weights, gradients and optimizer state partitioned (matrix region of the layout).  Weight
-zero3   all-gather, param_gather="stream" (default): one peer-gather kernel per transformer block on the
-        comm stream, one block ahead of the compute stream; "gemm" (K14): each matrix is gathered from the
-        owners' shards INSIDE the GEMM that consumes it (forward and again in dgrad).  K15 updates the local
-        shard; the vector tail (biases, LayerNorm) stays replicated like DeepSpeed's persistence threshold
-                                                                 [TH:231-237, zero3.json:10-27]
+zero3   all-gather, param_gather="gemm" (K14): no gather pass at all - the TMA producer of every consuming
+        GEMM (forward and dgrad) fetches each B tile straight from the owning rank's shard over NVLink and
+        multicasts it to the other CTAs of its thread-block cluster; "stream": one peer-gather kernel per
+        transformer block on the comm stream into local staging, one block ahead of the compute stream.
+        K15 updates the local shard; the vector tail (biases, LayerNorm) stays replicated like DeepSpeed's
+        persistence threshold                                    [TH:231-237, zero3.json:10-27]
 """
 from __future__ import annotations
 
@@ -39,7 +40,6 @@ from .parallel.collectives import DistCtx
 from .parallel.torch_engine import SHARDED_OPT, SHARDED_PARAMS, effective_grad_accum
 
 BF16 = torch.bfloat16
-BIG_SUFFIXES = ("attn.in_proj_weight", "attn.out_proj.weight", "mlp.0.weight", "mlp.2.weight")
 
 
 def _mix(*xs: int) -> int:
@@ -58,8 +58,9 @@ class NativeEngine:
                  seed: int = 42, param_gather: Optional[str] = None, nvtx: bool = False):
         self.ops = _ops.load()
         self.nvtx = bool(nvtx)                # host-side ranges: meaningful for eager steps and graph capture only
-        # fsdp / zero3 weight all-gather: "gemm" = gather warps inside the consuming GEMM (K14), "stream" = one
-        # peer-gather kernel per transformer block on the comm stream, one block ahead of the compute stream
+        # fsdp / zero3 weight all-gather: "gemm" = K14, every consuming GEMM fetches its B tiles from the owners'
+        # shards by TMA (cluster multicast), "stream" = one peer-gather kernel per transformer block on the comm
+        # stream, one block ahead of the compute stream
         # precedence: constructor argument, environment, strategy config file, default
         self.param_gather = (param_gather or os.environ.get("B200BENCH_PARAM_GATHER")
                              or getattr(cfg, "param_gather", None) or "stream")
@@ -75,8 +76,9 @@ class NativeEngine:
         self.V, self.d = model_cfg["vocab_size"], model_cfg["n_embd"]
         self.H, self.L = model_cfg["n_head"], model_cfg["n_layer"]
         self.hd = self.d // self.H
-        if self.hd != 64:
-            raise NotImplementedError("native attention kernels are built for head_dim 64")
+        if self.hd not in self.ops.attention_head_dims():
+            raise NotImplementedError(f"native attention kernels are built for head_dim "
+                                      f"{self.ops.attention_head_dims()}, got {self.hd}")
         if self.T > model_cfg["block_size"]:
             raise ValueError(f"Sequence {self.T} exceeds block size {model_cfg['block_size']}")
         self.M = self.B * self.T
@@ -164,12 +166,12 @@ class NativeEngine:
         self.dbig = e(M, 4 * d)
         self.dqkv = e(M, 3 * d)
         self.datt = e(M, d)
-        self.dq_acc = e(M, d, dt=torch.float32)
+        self.dq_acc = torch.zeros(M, d, dtype=torch.float32, device=dev)   # attention bwd leaves it zeroed again
         self.attD = e(self.B * self.H * self.T, dt=torch.float32)
-        sbytes = max(self.ops.colreduce_scratch_bytes(M, 4 * d, 1), self.ops.colreduce_scratch_bytes(M, d, 2),
-                     self.ops.colreduce_scratch_bytes(M, 3 * d, 1))
-        self.scratch = torch.zeros(sbytes // 4 + 64, dtype=torch.float32, device=dev)   # counters start at 0
-        self.scratch_side = torch.zeros(sbytes // 4 + 64, dtype=torch.float32, device=dev)
+        # fused LayerNorm backward: per-CTA fp32 partial column sums of the two LayerNorms of a block; the folds
+        # into dgamma / dbeta run on the side stream
+        self.ln_part = [torch.empty(self.ops.layernorm_bwd_fused_scratch_bytes(M, d) // 4, dtype=torch.float32,
+                                    device=dev) for _ in range(2)]
         # weight-gradient GEMMs and bias / LayerNorm-parameter reductions do not feed the backward chain:
         # they run on a side stream and fill the tail bubbles of the dgrad -> attention -> LN kernels
         self.side = torch.cuda.Stream(device=dev)
@@ -232,10 +234,6 @@ class NativeEngine:
         wte, wpe = Lt["transformer.wte.weight"], Lt["transformer.wpe.weight"]
         self.stage_wte = torch.empty(wte.numel, dtype=BF16, device=dev)
         self.stage_wpe = torch.empty(wpe.numel, dtype=BF16, device=dev)
-        # two staging buffers / flag arrays: GEMM k computes from slot k&1 while its gather warps
-        # prefetch the weight of GEMM k+1 into the other slot
-        self.stage_w = torch.empty(2, 4 * self.d * self.d, dtype=BF16, device=dev)
-        self.chunk_flags = torch.zeros(2, 1024, dtype=torch.int32, device=dev)
         # "stream" mode: whole-block staging slots, block l lives in slot l % n_slots.  Two slots = gather again
         # in backward (full re-sharding after forward).  L slots = every block stays resident until the end of the
         # micro-step: ZeRO-3 when the model fits stage3_max_live_parameters (zero3.json:11, DeepSpeed keeps such
@@ -260,14 +258,6 @@ class NativeEngine:
         self._invalidate_staging()
         # _slot_layer: block resident (or in flight) in each slot during this micro-step; _slot_done: comm-stream
         # event of the gather filling it; _slot_pending: the compute stream has not waited for that event yet
-        order = []
-        for l in range(self.L):
-            order += [f"transformer.h.{l}." + k for k in BIG_SUFFIXES]
-        for l in reversed(range(self.L)):
-            order += [f"transformer.h.{l}." + k for k in reversed(BIG_SUFFIXES)]
-        self._gorder = order
-        self._gseq = 0
-        self.gather_epoch = torch.zeros(1, dtype=torch.int32, device=dev)
         self.params = None
         self.P = {}
         for s in Lt:
@@ -280,30 +270,18 @@ class NativeEngine:
             # block matrices have no resident view: _w() hands out the staging slot per GEMM
 
     def _w(self, name: str):
-        """Weight matrix for the next GEMM: (tensor, K14 descriptor).  Resident weights: (P[name], None).
-        Sharded weights: the staging slot of this GEMM in the fixed per-micro-step order; the descriptor
-        tells the kernel whether to gather it itself (first GEMM only) and which weight to prefetch."""
+        """Weight matrix for the next GEMM: (tensor or shape, K14 peer descriptor).  Resident weights:
+        (P[name], None).  Sharded weights, "stream": the block's staging slot.  Sharded weights, "gemm" (K14):
+        only the shape - the GEMM's TMA producer fetches every tile from the owning rank's shard."""
         if not self.sharded_params:
             return self.P[name], None
+        s = self.layout[name]
         if self.param_gather == "stream":
-            s = self.layout[name]
             a, _ = self.layout.layer_range(s.layer)
             slot = s.layer % self.n_slots
             assert self._slot_layer[slot] == s.layer and not self._slot_pending[slot], (name, self._slot_layer)
             return self.stage_layer[slot][s.offset - a:s.offset - a + s.numel].view(s.shape), None
-        k = self._gseq
-        self._gseq += 1
-        assert self._gorder[k] == name, (k, name, self._gorder[k])
-        s = self.layout[name]
-        slot = k & 1
-        desc = dict(table=self.adj_table, ws=self.ctx.world_size, flat_off=s.offset, shard=self.S,
-                    rows=s.shape[0], cols=s.shape[1], flags=self.chunk_flags[slot], epoch=self.gather_epoch,
-                    self_gather=1 if k == 0 else 0)
-        if k + 1 < len(self._gorder):
-            n = self.layout[self._gorder[k + 1]]
-            desc.update(pf_flat_off=n.offset, pf_rows=n.shape[0], pf_cols=n.shape[1],
-                        pf_stage=self.stage_w[1 - slot], pf_flags=self.chunk_flags[1 - slot])
-        return self.stage_w[slot][:s.numel].view(s.shape), desc
+        return tuple(s.shape), dict(table=self.shard_pb.table, ws=self.ctx.world_size, flat_off=s.offset, shard=self.S)
 
     def _gather_block(self, l: int) -> None:
         """Queue the peer gather of block l's four matrices into its slot on the comm stream.  The comm
@@ -359,18 +337,18 @@ class NativeEngine:
             self._layer_begin(l, +1)
             o.layernorm_fwd(self.x[l], P[pre + "ln_1.weight"], P[pre + "ln_1.bias"], self.ln1[l], st[0], st[1])
             w, g = self._w(pre + "attn.in_proj_weight")
-            o.linear_fwd(self.ln1[l], w, self.qkv[l], bias=P[pre + "attn.in_proj_bias"], gather=g)
+            o.linear_fwd(self.ln1[l], w, self.qkv[l], bias=P[pre + "attn.in_proj_bias"], peer=g)
             o.attention_fwd(self.qkv[l], self.att[l], self.lse[l], B, T, H, hd, self.causal, p, self._seed(l, 1))
             w, g = self._w(pre + "attn.out_proj.weight")
             o.linear_fwd(self.att[l], w, self.xmid[l], bias=P[pre + "attn.out_proj.bias"], epi=_ops.EPI_BIAS_RESID,
-                         aux=self.x[l], gather=g)
+                         aux=self.x[l], peer=g)
             o.layernorm_fwd(self.xmid[l], P[pre + "ln_2.weight"], P[pre + "ln_2.bias"], self.ln2[l], st[2], st[3])
             w, g = self._w(pre + "mlp.0.weight")
             o.linear_fwd(self.ln2[l], w, self.pre[l], bias=P[pre + "mlp.0.bias"], epi=_ops.EPI_BIAS_GELU,
-                         out2=self.act[l], gather=g)
+                         out2=self.act[l], peer=g)
             w, g = self._w(pre + "mlp.2.weight")
             o.linear_fwd(self.act[l], w, self.x[l + 1], bias=P[pre + "mlp.2.bias"], epi=_ops.EPI_BIAS_RESID,
-                         aux=self.xmid[l], drop_p=p, seed=self._seed(l, 2), gather=g)
+                         aux=self.xmid[l], drop_p=p, seed=self._seed(l, 2), peer=g)
         o.layernorm_fwd(self.x[self.L], P["transformer.ln_f.weight"], P["transformer.ln_f.bias"], self.lnf,
                         self.statf[0], self.statf[1])
         o.linear_fwd(self.lnf, P["transformer.wte.weight"], self.logits)
@@ -379,13 +357,13 @@ class NativeEngine:
         """Run ``fn`` (kernels that only produce parameter gradients) on the side stream, ordered after
         everything issued so far on the current stream."""
         if not self.overlap_wgrad:
-            fn(self.scratch)
+            fn()
             return None
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self.side.wait_event(ev)
         with torch.cuda.stream(self.side):
-            fn(self.scratch_side)
+            fn()
         done = torch.cuda.Event()
         done.record(self.side)
         return done
@@ -409,54 +387,57 @@ class NativeEngine:
         o.cross_entropy(self.logits, self.targets, self.loss_rows, self.n_valid, self.loss, M, V,
                         grad_scale=1.0 / self.accum, write_grad=True)
         wte = P["transformer.wte.weight"]
+        drop = p > 0
         # lm_head: dlnf = dlogits @ wte ; dwte (+)= dlogits^T @ lnf      (tied weight)
-        self._on_side(lambda sc: o.linear_wgrad(self.logits, self.lnf, G["transformer.wte.weight"], accumulate=acc))
+        self._on_side(lambda: o.linear_wgrad(self.logits, self.lnf, G["transformer.wte.weight"], accumulate=acc))
         o.linear_dgrad(self.logits, wte, self.dln)
-        o.layernorm_bwd(self.dln, self.x[self.L], P["transformer.ln_f.weight"], self.statf[0], self.statf[1],
-                        self.dres)
-        o.layernorm_bwd_params(self.dln, self.x[self.L], self.statf[0], self.statf[1],
-                               G["transformer.ln_f.weight"], G["transformer.ln_f.bias"], self.scratch, acc)
+        # every LayerNorm backward is ONE launch: input gradient (+ residual gradient), gamma / beta gradients, and
+        # - when the block below ends in a dropout - the masked copy of the gradient that its fc2 GEMMs consume
+        o.layernorm_bwd_fused(self.dln, self.x[self.L], P["transformer.ln_f.weight"], self.statf[0], self.statf[1],
+                              self.dres, dx_drop=self.dy_drop if drop else None, drop_p=p,
+                              seed=self._seed(self.L - 1, 2), partials=self.ln_part[0])
+        self._on_side(lambda: o.layernorm_param_fold(self.ln_part[0], M, d, G["transformer.ln_f.weight"],
+                                                     G["transformer.ln_f.bias"], acc))
         for l in reversed(range(self.L)):
             pre = f"transformer.h.{l}."
             st = self.stats[l]
             # every buffer the side stream read for block l+1 is about to be overwritten
             self._join_side()
             self._layer_begin(l, -1)
-            # ---- MLP ----
-            dy = self.dres
-            if p > 0:
-                o.dropout_apply(self.dres, self.dy_drop, M, d, p, self._seed(l, 2))
-                dy = self.dy_drop
-            dy_read = self._on_side(lambda sc, dy=dy: (o.colsum(dy, G[pre + "mlp.2.bias"], sc, acc),
-                                                       o.linear_wgrad(dy, self.act[l], G[pre + "mlp.2.weight"],
-                                                                      accumulate=acc)))
+            # ---- MLP ----  (weight-gradient GEMMs also emit the bias gradient: row sums of dY^T in the same loop)
+            dy = self.dy_drop if drop else self.dres
+            dy_read = self._on_side(lambda dy=dy: o.linear_wgrad(dy, self.act[l], G[pre + "mlp.2.weight"],
+                                                                 accumulate=acc, dbias=G[pre + "mlp.2.bias"]))
             w, g = self._w(pre + "mlp.2.weight")
-            o.linear_dgrad(dy, w, self.dbig, epi=_ops.EPI_DGELU, aux=self.pre[l], gather=g)
-            self._on_side(lambda sc: (o.colsum(self.dbig, G[pre + "mlp.0.bias"], sc, acc),
-                                      o.linear_wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc)))
+            o.linear_dgrad(dy, w, self.dbig, epi=_ops.EPI_DGELU, aux=self.pre[l], peer=g)
+            self._on_side(lambda: o.linear_wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc,
+                                                 dbias=G[pre + "mlp.0.bias"]))
             w, g = self._w(pre + "mlp.0.weight")
-            o.linear_dgrad(self.dbig, w, self.dln2, gather=g)
-            o.layernorm_bwd(self.dln2, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid, dres=self.dres)
+            o.linear_dgrad(self.dbig, w, self.dln2, peer=g)
+            o.layernorm_bwd_fused(self.dln2, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid,
+                                  dres=self.dres, partials=self.ln_part[0])
             # ---- attention ----
-            self._on_side(lambda sc: (o.layernorm_bwd_params(self.dln2, self.xmid[l], st[2], st[3],
-                                                             G[pre + "ln_2.weight"], G[pre + "ln_2.bias"], sc, acc),
-                                      o.colsum(self.dmid, G[pre + "attn.out_proj.bias"], sc, acc),
-                                      o.linear_wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"],
-                                                     accumulate=acc)))
+            self._on_side(lambda: (o.layernorm_param_fold(self.ln_part[0], M, d, G[pre + "ln_2.weight"],
+                                                          G[pre + "ln_2.bias"], acc),
+                                   o.linear_wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"],
+                                                  accumulate=acc, dbias=G[pre + "attn.out_proj.bias"])))
             w, g = self._w(pre + "attn.out_proj.weight")
-            o.linear_dgrad(self.dmid, w, self.datt, gather=g)
+            # the out-proj dgrad writes dO and, from the same accumulator tile, D = rowsum(dO o O) per head
+            o.linear_dgrad(self.dmid, w, self.datt, epi=_ops.EPI_ROWDOT, aux=self.att[l], peer=g, rowdot=self.attD,
+                           rd_T=T, rd_hd=hd)
             o.attention_bwd(self.qkv[l], self.att[l], self.datt, self.lse[l], self.dqkv, self.attD, self.dq_acc,
-                            B, T, H, hd, self.causal, p, self._seed(l, 1))
-            self._on_side(lambda sc: (o.colsum(self.dqkv, G[pre + "attn.in_proj_bias"], sc, acc),
-                                      o.linear_wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"],
-                                                     accumulate=acc)))
+                            B, T, H, hd, self.causal, p, self._seed(l, 1), have_d=True, acc_is_zero=True)
+            self._on_side(lambda: o.linear_wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"],
+                                                 accumulate=acc, dbias=G[pre + "attn.in_proj_bias"]))
             w, g = self._w(pre + "attn.in_proj_weight")
-            o.linear_dgrad(self.dqkv, w, self.dln, gather=g)
-            if dy is self.dres and dy_read is not None:      # no dropout: the side stream read dres itself
+            o.linear_dgrad(self.dqkv, w, self.dln, peer=g)
+            if dy_read is not None:      # the fc2 weight gradient on the side stream is still entitled to read dy
                 torch.cuda.current_stream().wait_event(dy_read)
-            o.layernorm_bwd(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres, dres=self.dmid)
-            self._on_side(lambda sc: o.layernorm_bwd_params(self.dln, self.x[l], st[0], st[1], G[pre + "ln_1.weight"],
-                                                            G[pre + "ln_1.bias"], sc, acc))
+            o.layernorm_bwd_fused(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres,
+                                  dres=self.dmid, dx_drop=self.dy_drop if (drop and l > 0) else None, drop_p=p,
+                                  seed=self._seed(l - 1, 2), partials=self.ln_part[1])
+            self._on_side(lambda: o.layernorm_param_fold(self.ln_part[1], M, d, G[pre + "ln_1.weight"],
+                                                         G[pre + "ln_1.bias"], acc))
             a, b = self.layout.layer_range(l)
             if reduce_now:
                 # K13: this block's matrix gradients are final -> all-reduce them on the comm stream
@@ -469,7 +450,7 @@ class NativeEngine:
                         self._adamw_range(a, b)
             elif opt_now:
                 # single GPU: the block's wgrads were just queued on the side stream; its AdamW follows them
-                self._on_side(lambda sc: self._adamw_range(a, b))
+                self._on_side(lambda: self._adamw_range(a, b))
         self._join_side()       # lm_head wgrad must land before the embedding scatter-add onto the tied weight
         o.embedding_bwd(self.tokens, self.dres, G["transformer.wte.weight"], G["transformer.wpe.weight"],
                         B, T, d, p, self._seed(-1, 0), accumulate_wpe=acc)
@@ -490,7 +471,6 @@ class NativeEngine:
     def _micro_step(self, first_micro: bool, last_micro: bool) -> None:
         if self.dropout > 0:
             self.ops.step_seed_advance()      # new dropout masks every micro-step, also under graph replay
-        self._gseq = 0
         self._regather_tables = first_micro or not getattr(self, "keep_gathered", False)
         if self._regather_tables:
             self._invalidate_staging()      # weights moved at the optimizer boundary / slots were recycled
@@ -642,13 +622,11 @@ class NativeEngine:
             return e0.elapsed_time(e1) / reps
 
         def fwd():
-            self._gseq = 0
             self._regather_tables = True
             self._invalidate_staging()
             self._forward()
 
         def bwd():
-            self._gseq = 4 * self.L if self.sharded_params else 0
             self._invalidate_staging()
             self._loss_and_backward(True, True)
 

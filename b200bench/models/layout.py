@@ -15,6 +15,10 @@ from dataclasses import dataclass
 from typing import Dict, Iterator, List, Tuple
 
 ALIGN = 128  # elements; every tensor starts 256-byte aligned in bf16 (TMA needs 16 B)
+# K14 (parameter all-gather inside the consuming GEMM, csrc/gemm_sm100.cu): a B tile is fetched by TMA from the
+# rank that owns it, so no tile may straddle two owners.  Every matrix therefore starts on a multiple of
+# TILE_ROWS of its own rows, and the partition size is a multiple of TILE_ROWS rows of the widest matrix (4d).
+TILE_ROWS = 64
 
 
 @dataclass(frozen=True)
@@ -125,19 +129,27 @@ def build_layout(vocab_size: int, n_embd: int, n_head: int, n_layer: int, block_
         n = 1
         for s in shape:
             n *= s
+        if len(shape) == 2:                 # matrices: TILE_ROWS-row alignment in units of their own rows
+            q = TILE_ROWS * shape[1]
+            off = (off + q - 1) // q * q
         specs.append(ParamSpec(name, shape, off, n, layer, True))
         off = (off + n + ALIGN - 1) // ALIGN * ALIGN
 
     add("transformer.wte.weight", (vocab_size, d), -1)
     add("transformer.wpe.weight", (block_size, d), -1)
+    # blocks start on a TILE_ROWS boundary of the widest matrix, so that (for d a multiple of 256) the per-matrix
+    # alignment inside add() never pads between the four matrices of a block
+    q = TILE_ROWS * 4 * d
+    off = (off + q - 1) // q * q
     for i in range(n_layer):
         p = f"transformer.h.{i}."
         add(p + "attn.in_proj_weight", (3 * d, d), i)
         add(p + "attn.out_proj.weight", (d, d), i)
         add(p + "mlp.0.weight", (4 * d, d), i)
         add(p + "mlp.2.weight", (d, 4 * d), i)
-    # the sharded ("big") region ends here, padded so that it splits evenly over the ranks
-    quantum = ALIGN * max(1, world_size)
+    # the sharded ("big") region ends here, padded so that it splits evenly over the ranks into partitions that
+    # are whole TILE_ROWS-row groups of every matrix width (d and 4d)
+    quantum = TILE_ROWS * 4 * d * max(1, world_size)
     off = (off + quantum - 1) // quantum * quantum
     big_end = off
     for i in range(n_layer):

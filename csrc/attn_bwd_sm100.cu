@@ -399,18 +399,23 @@ attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ O, const __nv_bfloat16* _
   }
 }
 
-// dq_acc fp32 [M, d] -> bf16 into dqkv[:, 0:d] (row stride 3d)
+// dq_acc fp32 [M, d] -> bf16 into dqkv[:, 0:d] (row stride 3d).  The accumulator is zeroed again on the way
+// out, so the next backward call finds it ready and no memset pass is needed.
 __global__ void __launch_bounds__(256)
-attn_bwd_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int M,
+attn_bwd_dq_convert_kernel(float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int M,
                            int d) {
+  pdl_wait();
   const int nvec = d >> 3;
   const size_t total = static_cast<size_t>(M) * nvec;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const size_t m = i / nvec;
     const int c = static_cast<int>(i % nvec);
-    const float4 a = reinterpret_cast<const float4*>(acc + m * d)[2 * c];
-    const float4 bq = reinterpret_cast<const float4*>(acc + m * d)[2 * c + 1];
+    float4* src = reinterpret_cast<float4*>(acc + m * d) + 2 * c;
+    const float4 a = src[0];
+    const float4 bq = src[1];
+    src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
     uint4 u;
     u.x = pack_bf16x2(a.x, a.y);
     u.y = pack_bf16x2(a.z, a.w);
@@ -424,10 +429,10 @@ attn_bwd_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restr
 
 using namespace b200;
 
-extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* dout,
-                                  const float* lse, void* dqkv, float* D, float* dq_acc, int B,
-                                  int T, int H, int head_dim, int causal, float drop_p,
-                                  unsigned int seed, void* stream) {
+static int attention_bwd_impl(const void* qkv, const void* out, const void* dout,
+                              const float* lse, void* dqkv, float* D, float* dq_acc, int B,
+                              int T, int H, int head_dim, int causal, float drop_p,
+                              unsigned int seed, void* stream, int flags) {
   if (head_dim != AB_HD) return -5;
   const int d = H * head_dim;
   const int M = B * T;
@@ -446,8 +451,8 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done[dev & 63] = true;
   }
-  cudaMemsetAsync(dq_acc, 0, static_cast<size_t>(M) * d * sizeof(float), s);
-  {
+  if (!(flags & B200_ATTN_BWD_ACC_IS_ZERO)) cudaMemsetAsync(dq_acc, 0, static_cast<size_t>(M) * d * sizeof(float), s);
+  if (!(flags & B200_ATTN_BWD_HAVE_D)) {
     const long warps = static_cast<long>(M) * H;
     const int blocks = static_cast<int>((warps * 32 + 255) / 256);
     attn_bwd_prep_kernel<<<blocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(out),
@@ -494,8 +499,23 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* 
     size_t blocks = (work + 255) / 256;
     const size_t cap = static_cast<size_t>(device_sm_count()) * 8;
     if (blocks > cap) blocks = cap;
-    attn_bwd_dq_convert_kernel<<<static_cast<int>(blocks), 256, 0, s>>>(
-        dq_acc, static_cast<__nv_bfloat16*>(dqkv), M, d);
+    launch_pdl(attn_bwd_dq_convert_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, s, dq_acc,
+               static_cast<__nv_bfloat16*>(dqkv), M, d);
   }
   return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int b200_attention_bwd(const void* qkv, const void* out, const void* dout,
+                                  const float* lse, void* dqkv, float* D, float* dq_acc, int B,
+                                  int T, int H, int head_dim, int causal, float drop_p,
+                                  unsigned int seed, void* stream) {
+  return attention_bwd_impl(qkv, out, dout, lse, dqkv, D, dq_acc, B, T, H, head_dim, causal, drop_p, seed, stream, 0);
+}
+
+extern "C" int b200_attention_bwd_ex(const void* qkv, const void* out, const void* dout,
+                                     const float* lse, void* dqkv, float* D, float* dq_acc, int B,
+                                     int T, int H, int head_dim, int causal, float drop_p,
+                                     unsigned int seed, void* stream, int flags) {
+  return attention_bwd_impl(qkv, out, dout, lse, dqkv, D, dq_acc, B, T, H, head_dim, causal, drop_p, seed, stream,
+                            flags);
 }

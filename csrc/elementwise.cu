@@ -179,6 +179,208 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 }
 
 // ----------------------------------------------------------------------------------------
+// LayerNorm backward, everything in ONE pass over dy and x:
+//   dx      = rstd * (g*dy - mean(g*dy) - xhat*mean(g*dy*xhat)) [+ dres]
+//   dx_drop = dropout_mask(seed, row*d + col) * dx / (1-p)          (optional second output: the gradient of the
+//             fc2 output of the block below, whose dropout mask the GEMM epilogue drew with the same indexing)
+//   partial column sums of dy*xhat (dgamma) and dy (dbeta): one fp32 [2][d] row per CTA, folded by
+//   ln_param_fold_kernel (a few microseconds, off the critical path: only the optimizer needs its result)
+// A CTA owns 8*RPW consecutive rows; every warp loads its RPW rows (x, dy, dres) up front, so a CTA has all of its
+// DRAM requests in flight at once.  The column sums of the CTA are accumulated in shared memory - the warps take
+// turns, plain loads and stores in a fixed order, no atomics - so the result is deterministic.
+// ----------------------------------------------------------------------------------------
+struct LnBwdFused {
+  const __nv_bfloat16* dy;
+  const __nv_bfloat16* x;
+  const __nv_bfloat16* gamma;
+  const float* mean;
+  const float* rstd;
+  const __nv_bfloat16* dres;   // nullable
+  __nv_bfloat16* dx;
+  __nv_bfloat16* dx_drop;      // nullable
+  uint32_t drop_thr;
+  float drop_scale;
+  uint32_t drop_seed;
+  const uint32_t* seed_ptr;
+  float* partials;             // [ctas][2][d] in the shared-memory layout (see s_acc), nullable
+  int M, d;
+};
+
+template <int NV, int RPW>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_fused_kernel(const LnBwdFused p) {
+  pdl_wait();
+  // [2][2][d/8][4] floats: (dgamma | dbeta) x (elements 0-3 | 4-7 of each 8-column vector) - 16-byte lane stride,
+  // so the float4 accesses below are free of bank conflicts
+  extern __shared__ __align__(16) float s_acc[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int d = p.d, nvec = d >> 3;
+  const bool params = p.partials != nullptr;
+  if (params) {
+    for (int i = threadIdx.x; i < 2 * d; i += 256) s_acc[i] = 0.f;
+  }
+  const uint4* g4 = reinterpret_cast<const uint4*>(p.gamma);
+  uint32_t seed = p.drop_seed;
+  if (p.dx_drop && p.seed_ptr) seed ^= __ldg(p.seed_ptr);
+  constexpr bool PRELOAD_RES = NV <= 8;      // d = 4096: the residual gradient would not fit in registers as well
+  uint4 vx[RPW][NV], vd[RPW][NV], vr[RPW][PRELOAD_RES ? NV : 1];
+  float mean[RPW], rstd[RPW];
+  int rows[RPW];
+  // ---- every load of this warp's rows goes out before anything is consumed ----------------------------------
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    rows[r] = blockIdx.x * (8 * RPW) + r * 8 + warp;
+    const bool valid = rows[r] < p.M;
+    const size_t off = static_cast<size_t>(valid ? rows[r] : 0) * d;
+    const uint4* xr = reinterpret_cast<const uint4*>(p.x + off);
+    const uint4* dyr = reinterpret_cast<const uint4*>(p.dy + off);
+    const uint4* rr = reinterpret_cast<const uint4*>(p.dres + off);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      const bool ok = valid && c < nvec;
+      vx[r][i] = ok ? xr[c] : make_uint4(0, 0, 0, 0);
+      vd[r][i] = ok ? dyr[c] : make_uint4(0, 0, 0, 0);
+      if (PRELOAD_RES) vr[r][i] = (ok && p.dres) ? rr[c] : make_uint4(0, 0, 0, 0);
+    }
+    mean[r] = valid ? p.mean[rows[r]] : 0.f;
+    rstd[r] = valid ? p.rstd[rows[r]] : 0.f;
+  }
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) {
+        float fx[8], fd[8], g[8];
+        unpack8(vx[r][i], fx);
+        unpack8(vd[r][i], fd);
+        unpack8(__ldg(g4 + c), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float gd = g[j] * fd[j];
+          s1 += gd;
+          s2 += gd * (fx[j] - mean[r]) * rstd[r];
+        }
+      }
+    }
+    s1 = warp_sum(s1) / d;
+    s2 = warp_sum(s2) / d;
+    if (rows[r] < p.M) {
+      const size_t off = static_cast<size_t>(rows[r]) * d;
+      uint4* dxr = reinterpret_cast<uint4*>(p.dx + off);
+      uint4* dropr = p.dx_drop ? reinterpret_cast<uint4*>(p.dx_drop + off) : nullptr;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + i * 32;
+        if (c < nvec) {
+          float fx[8], fd[8], g[8], o[8], res[8];
+          unpack8(vx[r][i], fx);
+          unpack8(vd[r][i], fd);
+          if (PRELOAD_RES) unpack8(vr[r][i], res);
+          else unpack8(p.dres ? reinterpret_cast<const uint4*>(p.dres + off)[c] : make_uint4(0, 0, 0, 0), res);
+          unpack8(__ldg(g4 + c), g);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float xh = (fx[j] - mean[r]) * rstd[r];
+            o[j] = rstd[r] * (g[j] * fd[j] - s1 - xh * s2) + res[j];
+          }
+          const uint4 packed = pack8(o);
+          dxr[c] = packed;
+          if (dropr) {
+            float q[8];
+            unpack8(packed, q);      // mask the bf16 value that was stored, like a separate pass over dx would
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint64_t idx = static_cast<uint64_t>(rows[r]) * d + c * 8 + j;
+              q[j] = dropout_keep(seed, idx, p.drop_thr) ? q[j] * p.drop_scale : 0.f;
+            }
+            dropr[c] = pack8(q);
+          }
+        }
+      }
+    }
+  }
+  if (!params) return;
+  // ---- column sums over the CTA's rows: one turn per warp ------------------------------------------------------
+#pragma unroll 1
+  for (int turn = 0; turn < 8; ++turn) {
+    __syncthreads();
+    if (turn == warp) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + i * 32;
+        if (c < nvec) {
+          float cg[8], cb[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) cg[j] = cb[j] = 0.f;
+#pragma unroll
+          for (int r = 0; r < RPW; ++r) {
+            float fx[8], fd[8];
+            unpack8(vx[r][i], fx);
+            unpack8(vd[r][i], fd);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              cg[j] += fd[j] * ((fx[j] - mean[r]) * rstd[r]);
+              cb[j] += fd[j];
+            }
+          }
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            float4* ag = reinterpret_cast<float4*>(s_acc + h * (d >> 1) + c * 4);
+            float4* ab = reinterpret_cast<float4*>(s_acc + d + h * (d >> 1) + c * 4);
+            float4 a = *ag, b = *ab;
+            a.x += cg[4 * h + 0]; a.y += cg[4 * h + 1]; a.z += cg[4 * h + 2]; a.w += cg[4 * h + 3];
+            b.x += cb[4 * h + 0]; b.y += cb[4 * h + 1]; b.z += cb[4 * h + 2]; b.w += cb[4 * h + 3];
+            *ag = a;
+            *ab = b;
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  float4* mine = reinterpret_cast<float4*>(p.partials + static_cast<size_t>(blockIdx.x) * 2 * d);
+  for (int i = threadIdx.x; i < (2 * d) >> 2; i += 256) mine[i] = reinterpret_cast<const float4*>(s_acc)[i];
+}
+
+// Folds the per-CTA partial column sums [n][2][d] of layernorm_bwd_fused_kernel into dgamma / dbeta.
+// One CTA per 64 (stored) columns: 64 column lanes x 4 row groups, every thread keeps 8 loads in flight.
+__global__ void __launch_bounds__(256)
+ln_param_fold_kernel(const float* __restrict__ partials, int n, int d, __nv_bfloat16* __restrict__ dgamma,
+                     __nv_bfloat16* __restrict__ dbeta, int accumulate) {
+  pdl_wait();
+  __shared__ float red[4][64];
+  const int cl = threadIdx.x & 63, rg = threadIdx.x >> 6;
+  const int i = blockIdx.x * 64 + cl;              // index into the stored [2][d] layout
+  float s = 0.f;
+  if (i < 2 * d) {
+    int k = rg;
+    for (; k + 28 < n; k += 32) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(partials + static_cast<size_t>(k + 4 * u) * 2 * d + i);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) s += v[u];
+    }
+    for (; k < n; k += 4) s += __ldcg(partials + static_cast<size_t>(k) * 2 * d + i);
+  }
+  red[rg][cl] = s;
+  __syncthreads();
+  if (rg == 0 && i < 2 * d) {
+    s = (red[0][cl] + red[1][cl]) + (red[2][cl] + red[3][cl]);
+    // undo the shared-memory layout: i = which*d + half*(d/2) + c*4 + jj  ->  column c*8 + half*4 + jj
+    const int which = i / d, r = i - which * d;
+    const int half = r / (d >> 1), rr = r - half * (d >> 1);
+    const int col = (rr >> 2) * 8 + half * 4 + (rr & 3);
+    __nv_bfloat16* out = which ? dbeta : dgamma;
+    if (accumulate) s += __bfloat162float(out[col]);
+    out[col] = __float2bfloat16(s);
+  }
+}
+
+// ----------------------------------------------------------------------------------------
 // Column reductions over rows (bias gradients; LayerNorm gamma/beta gradients).
 // grid (ceil(N/256), R): block = 32 column-vectors x 8 row lanes, each thread owns 8 columns;
 // per-block partial sums -> scratch[R][K][N] (fp32); the last CTA of each column block to finish
@@ -669,6 +871,72 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
   return static_cast<int>(cudaGetLastError());
 }
 
+static inline int lnb_rows_per_cta(int d) { return (d <= 1024) ? 16 : 8; }   // two rows per warp while they fit in registers
+extern "C" size_t b200_layernorm_bwd_fused_scratch_bytes(int M, int d) {
+  const int rpc = lnb_rows_per_cta(d);
+  const size_t ctas = (M + rpc - 1) / rpc;
+  return ctas * 2 * static_cast<size_t>(d) * sizeof(float);
+}
+extern "C" int b200_layernorm_bwd_fused(const void* dy, const void* x, const void* gamma, const float* mean,
+                                        const float* rstd, const void* dres, void* dx, void* dx_drop,
+                                        float drop_p, unsigned int drop_seed, void* partials,
+                                        size_t partials_bytes, int M, int d, void* stream) {
+  if (d % 8) return -2;
+  const int rpc = lnb_rows_per_cta(d);
+  const int ctas = (M + rpc - 1) / rpc;
+  if (partials && partials_bytes < b200_layernorm_bwd_fused_scratch_bytes(M, d)) return -4;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  LnBwdFused p;
+  p.dy = static_cast<const __nv_bfloat16*>(dy);
+  p.x = static_cast<const __nv_bfloat16*>(x);
+  p.gamma = static_cast<const __nv_bfloat16*>(gamma);
+  p.mean = mean;
+  p.rstd = rstd;
+  p.dres = static_cast<const __nv_bfloat16*>(dres);
+  p.dx = static_cast<__nv_bfloat16*>(dx);
+  const uint32_t thr = drop_thr(drop_p);
+  p.dx_drop = thr ? static_cast<__nv_bfloat16*>(dx_drop) : nullptr;
+  p.drop_thr = thr;
+  p.drop_scale = thr ? 1.f / (1.f - drop_p) : 1.f;
+  p.drop_seed = drop_seed;
+  p.seed_ptr = step_seed_ptr();
+  p.partials = static_cast<float*>(partials);
+  p.M = M;
+  p.d = d;
+  const size_t smem = 2 * static_cast<size_t>(d) * sizeof(float);
+  const int nv = (d / 8 + 31) / 32;
+#define LNB_LAUNCH(NVV, RPW)                                                                                   \
+  do {                                                                                                         \
+    static bool attr_done[64] = {false};                                                                       \
+    int dev = 0;                                                                                               \
+    cudaGetDevice(&dev);                                                                                       \
+    if (smem > 48 * 1024 && !attr_done[dev & 63]) {                                                            \
+      cudaFuncSetAttribute(layernorm_bwd_fused_kernel<NVV, RPW>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                           131072);                                                                            \
+      attr_done[dev & 63] = true;                                                                              \
+    }                                                                                                          \
+    launch_pdl(layernorm_bwd_fused_kernel<NVV, RPW>, dim3(ctas), dim3(256), smem, s, p);                       \
+  } while (0)
+  if (nv <= 1) LNB_LAUNCH(1, 2);
+  else if (nv <= 2) LNB_LAUNCH(2, 2);
+  else if (nv <= 4) LNB_LAUNCH(4, 2);
+  else if (nv <= 8) LNB_LAUNCH(8, 1);
+  else if (nv <= 16) LNB_LAUNCH(16, 1);
+  else return -3;
+#undef LNB_LAUNCH
+  return static_cast<int>(cudaGetLastError());
+}
+/* dgamma / dbeta (+)= the partial column sums a b200_layernorm_bwd_fused call left in `partials` */
+extern "C" int b200_layernorm_param_fold(const void* partials, int M, int d, void* dgamma, void* dbeta,
+                                         int accumulate, void* stream) {
+  const int rpc = lnb_rows_per_cta(d);
+  const int n = (M + rpc - 1) / rpc;
+  launch_pdl(ln_param_fold_kernel, dim3((2 * d + 63) / 64), dim3(256), 0, static_cast<cudaStream_t>(stream),
+             static_cast<const float*>(partials), n, d, static_cast<__nv_bfloat16*>(dgamma),
+             static_cast<__nv_bfloat16*>(dbeta), accumulate);
+  return static_cast<int>(cudaGetLastError());
+}
+
 extern "C" size_t b200_colreduce_scratch_bytes(int M, int N, int outputs) {
   // 256 completion counters (one per 256-column block, fixed place at the head of the buffer so that
   // calls with different shapes can share one scratch buffer) + fp32 partials [splits][outputs][N]
@@ -826,7 +1094,9 @@ extern "C" int b200_step_seed_advance(void* stream) {
 // In host code the name of a __device__ array is only a host-side stand-in for the symbol, not a
 // device address, so it cannot be handed to a kernel; the address is looked up with
 // cudaGetSymbolAddress once per device, with that device current, on the FIRST call made on that
-// device.  Make that first call before any stream capture starts.
+// device.  Make that first call before any stream capture starts.  The per-device address cache is written
+// without a lock: two host threads that make the first call on the same device at the same moment both store
+// the same address, which is harmless.
 //
 // The array is shared by every call and keeps whatever the previous call left in it.  The completion
 // counters at its head must be zero when the kernel starts, so they are cleared on the caller's

@@ -13,16 +13,26 @@
 //
 // Structure: persistent, warp-specialised CTA of 192 threads, one CTA per SM.
 //   warp 0      TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
-//   warp 1      MMA issuer    (one elected lane: tcgen05.mma cta_group::1, M=128, N=BN, K=16)
-//   warps 2..5  epilogue      (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+//   warp 1      MMA issuer    (one elected lane: tcgen05.mma, M=128 (256 for a CTA pair), N=BN, K=16)
+//   warps 2..5  epilogue      (tcgen05.ld 32x32b -> registers -> fused epilogue -> smem -> TMA store)
 // Two accumulator stages in TMEM (2*BN columns) let the epilogue of tile i overlap the main
 // loop of tile i+1.
+//
+// K14 (the FSDP / ZeRO-3 parameter all-gather, TH:229-237,366) lives in the producer warp:
+// when B is a weight matrix that is partitioned over ranks, there is one tensor map per OWNING rank over
+// that rank's shard as mapped into this process (peer memory over NVLink), and every B tile is fetched by
+// TMA straight from its owner into shared memory - no gather pass, no staging copy in HBM, no flags.  Peer
+// data is not cached by the local L2, so the CTAs (or CTA pairs) that work on the same N-tile for different
+// M-tiles form ONE thread-block cluster: each of them fetches 1/P of the B tile and multicasts it to the
+// others (.multicast::cluster), so a remote tile crosses NVLink once per cluster, not once per CTA.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
+#include <mutex>
 #include <type_traits>
 
 #include "b200_internal.h"
@@ -33,28 +43,8 @@ namespace b200 {
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
 constexpr int GEMM_THREADS = 192;
-constexpr int GEMM_GATHER_THREADS = 64;    // 2 extra warps in gather mode (256 threads total: no register cap below 255)
-
-__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* addr) {
-  uint32_t v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu_u32(uint32_t* addr, uint32_t v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* addr) {
-  uint4 v;
-  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(addr)
-               : "memory");
-  return v;
-}
-// generic-proxy global writes/reads <-> async-proxy (TMA) accesses of the same global memory
-__device__ __forceinline__ void fence_proxy_async_global() {
-  asm volatile("fence.proxy.async.global;" ::: "memory");
-}
+constexpr int GEMM_MAX_OWNERS = 8;
+constexpr int GEMM_MAX_UNITS = 8;       // tile units (CTAs or CTA pairs) per cluster that share B by multicast
 
 template <int BN, int CTAS>
 struct GemmCfg {
@@ -62,12 +52,20 @@ struct GemmCfg {
   static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;  // 16 KiB
   static constexpr int kBBytes = kBNLocal * GEMM_BK * 2;
   static constexpr int kStagingBytes = 32768;            // TMA-store staging of the epilogue
-  static constexpr int kBarBytes = 256 + 2 * BN * 4;     // barriers + double-buffered fp32 bias slice
+  // barriers (256 B) + 2 KiB that hold either the double-buffered fp32 bias slice (2 x BN floats) or, for a
+  // weight-gradient GEMM that also produces the bias gradient, the all-ones B tile of the row-sum MMA
+  static constexpr int kBarBytes = 256 + 2048;
   static constexpr int kRing = 232448 - kStagingBytes - kBarBytes;   // what is left of the 227 KiB
   static constexpr int kStages = (kRing / (kABytes + kBBytes)) > 8 ? 8 : (kRing / (kABytes + kBBytes));
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN;  // 256 or 512, power of two
+  static constexpr int kBiasCol = 2 * BN - 32;   // row-sum accumulator (16 columns) of the bias-gradient mode
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + kBarBytes;
+  static_assert(2 * BN * 4 <= 2048, "bias slice must fit its 2 KiB");
+};
+
+struct BMaps {
+  CUtensorMap m[GEMM_MAX_OWNERS];
 };
 
 struct GemmParams {
@@ -83,46 +81,46 @@ struct GemmParams {
   uint32_t drop_threshold;      // p * 2^32, 0 = no dropout
   uint32_t drop_seed;
   const uint32_t* seed_ptr;     // per-step seed word in device memory (nullable)
-  int num_m_tiles, num_n_tiles;
-  // ---- K14: all-gather of the B operand fused into this GEMM (gather_ws == 0: off) -------------
-  // B (a weight matrix, row-major [g_rows, g_cols]) is partitioned over ranks by flat offset; four
-  // extra warps per CTA pull it chunk by chunk (g_chunk_rows rows each) from the owners' shards over
-  // NVLink into the local staging buffer that the TMA descriptor of B points at, and publish one flag
-  // per chunk; the TMA producer waits for the chunks a tile needs.  Transfer overlaps the math.
-  int gather_ws;
-  int g_rows, g_cols, g_chunk_rows;
-  unsigned long long g_flat_off;     // flat-layout offset of B[0,0]
-  unsigned long long g_shard;        // elements per rank partition
-  const __nv_bfloat16* g_src[8];     // per rank: partition base MINUS rank*g_shard (flat-indexed)
-  __nv_bfloat16* g_dst;              // staging buffer (== B)
-  uint32_t* g_flags;                 // [chunks] ready flags
-  const uint32_t* g_epoch;           // device word E, bumped after every gather-GEMM
-  int g_self;                        // 1: gather B in this kernel (flags <- E+1); 0: a previous kernel prefetched it
-  // prefetch job: the NEXT GEMM's weight, pulled into its staging buffer while this GEMM computes
-  // (flags <- E+2).  pf_rows == 0: none.   [FSDP forward_prefetch / backward_prefetch]
-  int pf_rows, pf_cols;
-  unsigned long long pf_flat_off;
-  __nv_bfloat16* pf_dst;
-  uint32_t* pf_flags;
+  int num_m_tiles, num_n_tiles; // tiles of a whole CLUSTER: (units * CTAS * 128) rows x BN columns
+  int units;                    // P: tile units per cluster along M; B is multicast across them (1 = off)
+  // ---- K14: B partitioned over owning ranks.  Row r of B lives in owner (b_row0 + r) / b_rows_per_owner at
+  // local row (b_row0 + r) % b_rows_per_owner of that owner's shard, viewed as a [rows_per_owner, ldb] matrix.
+  int b_ws;                     // number of owners (<= 1: B is one local matrix)
+  uint32_t b_row0, b_rows_per_owner;
+  // ---- weight-gradient extras: dbias[m] (+)= sum_k A[m,k]  (the bias gradient is the row sum of dY^T)
+  __nv_bfloat16* dbias;
+  int dbias_accum;
+  // ---- B200_EPI_ROWDOT: D = acc and rowdot[(b*H + h)*T + t] = sum_{c in head h} acc[m,c] * aux[m,c], m = b*T + t
+  float* rowdot;
+  int rd_T, rd_hd;
 };
 
 // CTAS = 1: one CTA per 128 x BN tile (cta_group::1).
-// CTAS = 2: a CTA pair (2-CTA cluster) per 256 x BN tile (cta_group::2): each CTA stages its own 128 rows
+// CTAS = 2: a CTA pair per 256 x BN tile (cta_group::2): each CTA stages its own 128 rows
 //           of A and HALF of B, the leader issues M=256 MMAs that read both halves, so the shared-memory
-//           traffic per MAC halves for B — at 128x128 per CTA the single-CTA kernel is shared-memory-bound
+//           traffic per MAC halves for B - at 128x128 per CTA the single-CTA kernel is shared-memory-bound
 //           (operand reads + TMA fills = 2 x 128 B/clk), which caps it near 50 % of the tensor peak.
+// A cluster holds p.units such tile units (consecutive M-tiles of one N-tile).
 template <int BN, int CTAS>
-__global__ void __launch_bounds__(GEMM_THREADS + GEMM_GATHER_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
-                         const __grid_constant__ CUtensorMap map_b,
+                         const __grid_constant__ BMaps maps_b,
                          const __grid_constant__ CUtensorMap map_d,
                          const __grid_constant__ CUtensorMap map_d2, const GemmParams p) {
   using Cfg = GemmCfg<BN, CTAS>;
   constexpr int BNL = Cfg::kBNLocal;
-  const uint32_t cta_rank = (CTAS == 2) ? cluster_ctarank() : 0u;
+  const int P = p.units;
+  const int CL = P * CTAS;                                  // CTAs per cluster
+  const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
+  const uint32_t cta_rank = crank % CTAS;                   // which half of a pair
+  const uint32_t unit_in_cl = crank / CTAS;
   const bool is_leader = cta_rank == 0;
-  const int unit = blockIdx.x / CTAS;          // tile-scheduling unit: a CTA or a CTA pair
-  const int num_units = gridDim.x / CTAS;
+  const int cluster_id = blockIdx.x / CL;
+  const int num_clusters = gridDim.x / CL;
+  const uint16_t mask_all = static_cast<uint16_t>((1u << CL) - 1u);
+  const uint16_t mask_unit = static_cast<uint16_t>(CTAS == 2 ? (3u << (crank & ~1u)) : (1u << crank));
+  uint16_t mask_half = 0;                                   // every CTA that holds the same half of B as this one
+  for (int u = 0; u < P; ++u) mask_half |= static_cast<uint16_t>(1u << (u * CTAS + cta_rank));
   // SWIZZLE_128B tiles need 1024-byte alignment; declaring the alignment (instead of rounding the
   // pointer up through an integer) keeps the address space known, so accesses are LDS/STS.
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -135,19 +133,22 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   uint64_t* tfull_bar = bars + 2 * Cfg::kStages;     // [2]
   uint64_t* tempty_bar = bars + 2 * Cfg::kStages + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * Cfg::kStages + 4);
+  uint8_t* aux_smem = reinterpret_cast<uint8_t*>(bars) + 256;   // 2 KiB: bias slice or the all-ones tile
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const bool bias_grad = p.dbias != nullptr;
+  const int nacc = bias_grad ? 1 : 2;   // bias-gradient mode gives the second accumulator stage to the row sums
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
-    tma_prefetch_desc(&map_b);
+    for (int o = 0; o < (p.b_ws > 1 ? p.b_ws : 1); ++o) tma_prefetch_desc(&maps_b.m[o]);
     tma_prefetch_desc(&map_d);
     for (int s = 0; s < Cfg::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], P);     // one commit per tile unit of the cluster that read the slot
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
@@ -158,9 +159,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 1) {
     if (CTAS == 2) tmem_alloc_2cta(tmem_slot, Cfg::kTmemCols); else tmem_alloc(tmem_slot, Cfg::kTmemCols);
   }
+  if (bias_grad) {   // B operand of the row-sum MMA: bf16 1.0 everywhere, so layout and swizzle do not matter
+    for (int i = threadIdx.x; i < 512; i += GEMM_THREADS) reinterpret_cast<uint32_t*>(aux_smem)[i] = 0x3F803F80u;
+    fence_proxy_async();
+  }
   tc_fence_before();
   __syncthreads();
-  if (CTAS == 2) cluster_sync_all();   // the peer's barriers are initialised before anyone signals them
+  if (CL > 1) cluster_sync_all();   // the peers' barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // Everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the tail of the
@@ -170,158 +175,194 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    // (the whole warp walks the loop with warp-uniform values; one elected lane issues the copies)
+    {
       int stage = 0;
       uint32_t phase = 0;
-      const bool gather = p.gather_ws > 0;
-      // own weight: published as E+1 either by this kernel's gather warps or by the previous kernel's
-      // prefetch (whose epoch was E-1).  Zero-filled flags can never satisfy the wait.
-      const uint32_t g_want = gather ? *p.g_epoch + 1u : 0u;
-      bool g_all_ready = false;
-      auto wait_chunk = [&](int c) {
-        uint32_t spins = 0;
-        while (static_cast<int32_t>(ld_acquire_gpu_u32(p.g_flags + c) - g_want) < 0) {
-          if (++spins > (1u << 28)) __trap();
+      // This thread's instruction count per k-block is on the critical path of the whole pipeline (it has to stay
+      // under the ~512 cycles the tensor cores need per k-block), so everything that does not change with k is
+      // resolved per tile: slice offsets, and for a partitioned B the owner and the local row in its shard.
+      const bool remote = p.b_ws > 1;
+      const int sr = BNL / P;            // K-major B: rows of this CTA's half that this unit fetches for everybody
+      const int kr = GEMM_BK / P;        // MN-major B: k-rows of every 64-column chunk that this unit fetches
+      const int b_dst_off = static_cast<int>(unit_in_cl) * (p.b_mn ? kr : sr) * 128;
+      const int b_row_add = static_cast<int>(unit_in_cl) * (p.b_mn ? kr : sr);
+      auto issue_b = [&](const CUtensorMap* m, void* dst, int c0, int lrow) {
+        if (P > 1) {
+          if (CTAS == 2) tma_load_2d_2cta_mc(m, &full_bar[stage], dst, c0, lrow, mask_half);
+          else tma_load_2d_mc(m, &full_bar[stage], dst, c0, lrow, mask_half);
+        } else {
+          if (CTAS == 2) tma_load_2d_2cta(m, &full_bar[stage], dst, c0, lrow);
+          else tma_load_2d(m, &full_bar[stage], dst, c0, lrow);
         }
       };
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
-        const int m0 = (tile % p.num_m_tiles) * (GEMM_BM * CTAS) + static_cast<int>(cta_rank) * GEMM_BM;
+      // owner of B row `row` and the row's index inside that owner's shard
+      auto resolve = [&](int row, uint32_t& owner, int& lrow) {
+        const uint32_t g = p.b_row0 + static_cast<uint32_t>(row);
+        owner = g / p.b_rows_per_owner;
+        if (owner >= static_cast<uint32_t>(p.b_ws)) owner = p.b_ws - 1;    // past the end: out of the map -> zeros
+        lrow = static_cast<int>(g - owner * p.b_rows_per_owner);
+      };
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int m0 = (tile % p.num_m_tiles) * (GEMM_BM * CL) + static_cast<int>(crank) * GEMM_BM;
         const int n0 = (tile / p.num_m_tiles) * BN + static_cast<int>(cta_rank) * BNL;   // this CTA's B rows
-        if (gather && !p.b_mn) {   // B rows = n: this CTA needs the chunks covering [n0, n0+BNL)
-          const int n1 = (n0 + BNL < p.g_rows ? n0 + BNL : p.g_rows) - 1;
-          for (int c = n0 / p.g_chunk_rows; c <= n1 / p.g_chunk_rows; ++c) wait_chunk(c);
-          fence_proxy_async_global();
+        const CUtensorMap* mb = &maps_b.m[0];
+        uint32_t owner = 0;
+        int brow = (p.b_mn ? 0 : n0) + b_row_add;       // K-major: fixed per tile; MN-major: advances with k
+        if (remote) {
+          resolve(brow, owner, brow);
+          mb = &maps_b.m[owner];
         }
         for (int kb = 0; kb < num_kb; ++kb) {
-          if (gather && p.b_mn && !g_all_ready) {   // B rows = k: one chunk per k-block, first tile only
-            const int r0 = kb * GEMM_BK;
-            const int r1 = (r0 + GEMM_BK < p.g_rows ? r0 + GEMM_BK : p.g_rows) - 1;
-            for (int c = r0 / p.g_chunk_rows; c <= r1 / p.g_chunk_rows; ++c) wait_chunk(c);
-            fence_proxy_async_global();
-          }
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = tiles + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          // pair mode: all bytes (of both CTAs) are credited to the leader's barrier; only it arrives
-          if (is_leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           const int k0 = kb * GEMM_BK;
-          auto load = [&](const CUtensorMap* m, void* dst, int c0, int c1) {
-            if (CTAS == 2) tma_load_2d_2cta(m, &full_bar[stage], dst, c0, c1);
-            else tma_load_2d(m, &full_bar[stage], dst, c0, c1);
-          };
-          if (!p.a_mn) {
-            load(&map_a, sa, k0, m0);
-          } else {
+          if (elect_one()) {
+            // pair mode: all bytes (of both CTAs) are credited to the leader's barrier; only it arrives
+            if (is_leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
+            auto load_a = [&](void* dst, int c0, int c1) {
+              if (CTAS == 2) tma_load_2d_2cta(&map_a, &full_bar[stage], dst, c0, c1);
+              else tma_load_2d(&map_a, &full_bar[stage], dst, c0, c1);
+            };
+            if (!p.a_mn) {
+              load_a(sa, k0, m0);
+            } else {
 #pragma unroll
-            for (int c = 0; c < GEMM_BM / 64; ++c) load(&map_a, sa + c * (GEMM_BK * 128), m0 + 64 * c, k0);
+              for (int c = 0; c < GEMM_BM / 64; ++c) load_a(sa + c * (GEMM_BK * 128), m0 + 64 * c, k0);
+            }
+            if (!p.b_mn) {
+              // K-major B: this CTA's BNL rows; with multicast each unit fetches BNL/P of them for everybody
+              issue_b(mb, sb + b_dst_off, k0, brow);
+            } else {
+              // MN-major B: 64 k-rows x 64 n-columns per chunk; with multicast each unit fetches 64/P k-rows
+#pragma unroll
+              for (int c = 0; c < BNL / 64; ++c)
+                issue_b(mb, sb + c * (GEMM_BK * 128) + b_dst_off, n0 + 64 * c, brow);
+            }
           }
-          if (!p.b_mn) {
-            load(&map_b, sb, k0, n0);
-          } else {
-#pragma unroll
-            for (int c = 0; c < BNL / 64; ++c) load(&map_b, sb + c * (GEMM_BK * 128), n0 + 64 * c, k0);
+          __syncwarp();
+          if (p.b_mn) {
+            brow += GEMM_BK;
+            if (remote && brow >= static_cast<int>(p.b_rows_per_owner) && owner + 1 < static_cast<uint32_t>(p.b_ws)) {
+              brow -= static_cast<int>(p.b_rows_per_owner);     // the next k-block belongs to the next owner
+              mb = &maps_b.m[++owner];
+            }
           }
           if (++stage == Cfg::kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        g_all_ready = true;
       }
-    }
-  } else if (warp >= 6) {
-    // ================================ K14 gather warps =============================
-    if (p.gather_ws > 0) {
-      const int gt = threadIdx.x - GEMM_THREADS;   // 0..63
-      const uint32_t E = *p.g_epoch;
-      auto gather_job = [&](unsigned long long flat_off, int rows, int cols, __nv_bfloat16* out,
-                            uint32_t* flags, uint32_t publish) {
-        const size_t chunk_elems = static_cast<size_t>(p.g_chunk_rows) * cols;
-        const size_t total = static_cast<size_t>(rows) * cols;
-        const int nchunks = (rows + p.g_chunk_rows - 1) / p.g_chunk_rows;
-        for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
-          size_t e = c * chunk_elems;
-          const size_t e1 = (e + chunk_elems < total) ? e + chunk_elems : total;
-          while (e < e1) {
-            const size_t flat = flat_off + e;
-            const int owner = static_cast<int>(flat / p.g_shard);
-            const size_t seg_end = static_cast<size_t>(owner + 1) * p.g_shard - flat_off;
-            const size_t e_stop = seg_end < e1 ? seg_end : e1;
-            const uint4* src = reinterpret_cast<const uint4*>(p.g_src[owner] + flat);
-            uint4* dst = reinterpret_cast<uint4*>(out + e);
-            const size_t nvec = (e_stop - e) >> 3;
-            // 8 independent 16-byte loads per thread in flight: NVLink latency is hidden by depth
-            for (size_t i = gt; i < nvec; i += 8 * GEMM_GATHER_THREADS) {
-              uint4 v[8];
-#pragma unroll
-              for (int u = 0; u < 8; ++u)
-                if (i + u * GEMM_GATHER_THREADS < nvec) v[u] = ld_volatile_v4(src + i + u * GEMM_GATHER_THREADS);
-#pragma unroll
-              for (int u = 0; u < 8; ++u)
-                if (i + u * GEMM_GATHER_THREADS < nvec) dst[i + u * GEMM_GATHER_THREADS] = v[u];
-            }
-            e = e_stop;
-          }
-          __threadfence();
-          fence_proxy_async_global();
-          asm volatile("bar.sync 2, 64;" ::: "memory");
-          if (gt == 0) st_release_gpu_u32(flags + c, publish);
-        }
-      };
-      if (p.g_self) gather_job(p.g_flat_off, p.g_rows, p.g_cols, p.g_dst, p.g_flags, E + 1u);  // urgent: this GEMM waits on it
-      if (p.pf_rows > 0) gather_job(p.pf_flat_off, p.pf_rows, p.pf_cols, p.pf_dst, p.pf_flags, E + 2u);
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0 && is_leader) {
+    if (is_leader) {
+      // The whole warp walks the loop (warp-uniform control flow and values, so the compiler keeps descriptors and
+      // counters in uniform registers); one elected lane issues.
+      // The issue rate of this single thread bounds the whole kernel (four MMAs of 128 tensor-core cycles each per
+      // k-block), so the loop body is kept to a few adds per MMA: the shared-memory descriptors of stage 0 are
+      // built once, and stage / k-step offsets are added to their address field (bits [0,14), units of 16 bytes;
+      // a CTA's shared memory is < 2^18 bytes, so the add never carries out of the field).
       const uint32_t idesc = umma_idesc_bf16(GEMM_BM * CTAS, BN, p.a_mn != 0, p.b_mn != 0);
+      const uint32_t idesc_rowsum = umma_idesc_bf16(GEMM_BM * CTAS, 16, p.a_mn != 0, false);
       // K-major: +32 B per 16-element K step inside the 128 B swizzle row.
       // MN-major: +16 k-rows * 128 B = 2048 B per K step; MN chunks are BK*128 B apart.
-      const uint32_t a_kstep = p.a_mn ? 2048u : 32u;
-      const uint32_t b_kstep = p.b_mn ? 2048u : 32u;
-      const uint32_t a_lbo = p.a_mn ? GEMM_BK * 128u : 16u;
-      const uint32_t b_lbo = p.b_mn ? GEMM_BK * 128u : 16u;
+      const uint32_t a_k = (p.a_mn ? 2048u : 32u) >> 4;
+      const uint32_t b_k = (p.b_mn ? 2048u : 32u) >> 4;
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(tiles), p.a_mn ? GEMM_BK * 128u : 16u, 1024);
+      const uint64_t bdesc0 = umma_smem_desc(smem_u32(tiles) + Cfg::kABytes, p.b_mn ? GEMM_BK * 128u : 16u, 1024);
+      const uint64_t odesc0 = umma_smem_desc(smem_u32(aux_smem), 16, 1024);   // all-ones tile, +2 units per k-step
+      constexpr uint32_t kStageUnits = Cfg::kStageBytes >> 4;
+      const uint16_t empty_mask = (P > 1) ? mask_all : mask_unit;
+      auto commit_empty = [&](uint64_t* bar) {
+        // smem slot reusable (in every CTA of the cluster that fed it) once the MMAs issued so far retire
+        if (CTAS == 2) umma_commit_2cta(bar, empty_mask);
+        else if (P > 1) umma_commit_mc(bar, empty_mask);
+        else umma_commit(bar);
+      };
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const bool rowsum = bias_grad && (tile / p.num_m_tiles) == 0;   // one N-tile is enough for the row sums
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(tiles + stage * Cfg::kStageBytes);
-          const uint32_t sb = sa + Cfg::kABytes;
-#pragma unroll
-          for (int k = 0; k < GEMM_BK / 16; ++k) {
-            const uint64_t adesc = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
-            const uint64_t bdesc = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
-            if (CTAS == 2) umma_bf16_ss_2cta(tmem_d, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
-            else umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+        if (!rowsum) {
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint64_t ad = adesc0 + static_cast<uint32_t>(stage) * kStageUnits;
+            const uint64_t bd = bdesc0 + static_cast<uint32_t>(stage) * kStageUnits;
+            if (elect_one()) {
+              if (CTAS == 2) {
+                umma_bf16_ss_2cta(tmem_d, ad, bd, idesc, kb ? 1u : 0u);
+                umma_bf16_ss_2cta(tmem_d, ad + a_k, bd + b_k, idesc, 1u);
+                umma_bf16_ss_2cta(tmem_d, ad + 2 * a_k, bd + 2 * b_k, idesc, 1u);
+                umma_bf16_ss_2cta(tmem_d, ad + 3 * a_k, bd + 3 * b_k, idesc, 1u);
+              } else {
+                umma_bf16_ss(tmem_d, ad, bd, idesc, kb ? 1u : 0u);
+                umma_bf16_ss(tmem_d, ad + a_k, bd + b_k, idesc, 1u);
+                umma_bf16_ss(tmem_d, ad + 2 * a_k, bd + 2 * b_k, idesc, 1u);
+                umma_bf16_ss(tmem_d, ad + 3 * a_k, bd + 3 * b_k, idesc, 1u);
+              }
+              commit_empty(&empty_bar[stage]);
+            }
+            __syncwarp();
+            if (++stage == Cfg::kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
-          // smem slot reusable (in both CTAs of a pair) once these MMAs retire
-          if (CTAS == 2) umma_commit_2cta(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
-          if (++stage == Cfg::kStages) {
-            stage = 0;
-            phase ^= 1;
+        } else {
+          // weight gradient + bias gradient: [128 x 16] += A[128 x 16k] * ones, every column = the row sum of A
+          const uint32_t tmem_rs = tmem_base + Cfg::kBiasCol;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint64_t ad = adesc0 + static_cast<uint32_t>(stage) * kStageUnits;
+            const uint64_t bd = bdesc0 + static_cast<uint32_t>(stage) * kStageUnits;
+            if (elect_one()) {
+#pragma unroll
+              for (uint32_t k = 0; k < GEMM_BK / 16; ++k) {
+                const uint32_t accf = (kb | k) ? 1u : 0u;
+                if (CTAS == 2) {
+                  umma_bf16_ss_2cta(tmem_d, ad + k * a_k, bd + k * b_k, idesc, accf);
+                  umma_bf16_ss_2cta(tmem_rs, ad + k * a_k, odesc0 + 2 * k, idesc_rowsum, accf);
+                } else {
+                  umma_bf16_ss(tmem_d, ad + k * a_k, bd + k * b_k, idesc, accf);
+                  umma_bf16_ss(tmem_rs, ad + k * a_k, odesc0 + 2 * k, idesc_rowsum, accf);
+                }
+              }
+              commit_empty(&empty_bar[stage]);
+            }
+            __syncwarp();
+            if (++stage == Cfg::kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
         // accumulator complete -> epilogue (of both CTAs)
-        if (CTAS == 2) umma_commit_2cta(&tfull_bar[acc]); else umma_commit(&tfull_bar[acc]);
-        if (++acc == 2) {
+        if (elect_one()) {
+          if (CTAS == 2) umma_commit_2cta(&tfull_bar[acc], mask_unit); else umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++acc == nacc) {
           acc = 0;
           acc_phase ^= 1;
         }
       }
     }
-  } else if (warp < 6) {
+  } else {
     // ================================ epilogue ====================================
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
     const int et = threadIdx.x - 64;   // 0..127 among the epilogue threads
     const uint32_t seed = p.drop_seed ^ ((p.drop_threshold && p.seed_ptr) ? __ldg(p.seed_ptr) : 0u);
-    float* s_bias = reinterpret_cast<float*>(tmem_slot + 4);   // [2][BN] floats, double-buffered per tile
+    float* s_bias = reinterpret_cast<float*>(aux_smem);   // [2][BN] floats, double-buffered per tile
     int acc = 0;
     uint32_t acc_phase = 0;
     int tile_no = 0;
@@ -337,7 +378,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     auto run_tile = [&](auto epi_c, int m0, int n0, const float* bias_s) {
       constexpr int EPI = decltype(epi_c)::value;
       constexpr bool HAS_BIAS = (EPI == B200_EPI_BIAS || EPI == B200_EPI_BIAS_GELU || EPI == B200_EPI_BIAS_RESID);
-      constexpr bool HAS_AUX = (EPI == B200_EPI_BIAS_RESID || EPI == B200_EPI_DGELU || EPI == B200_EPI_ACCUM);
+      constexpr bool HAS_AUX = (EPI == B200_EPI_BIAS_RESID || EPI == B200_EPI_DGELU || EPI == B200_EPI_ACCUM ||
+                                EPI == B200_EPI_ROWDOT);
       constexpr bool DUAL = (EPI == B200_EPI_BIAS_GELU);
       const int row = m0 + quarter * 32 + lane;
       const bool row_ok = row < p.M;
@@ -358,6 +400,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       load_aux(0, aux_cur);
       uint8_t* buf0 = nullptr;
       uint8_t* buf1 = nullptr;
+      float dot = 0.f;                       // B200_EPI_ROWDOT: running sum over the columns of one head
+      const int rd_mask = (EPI == B200_EPI_ROWDOT) ? (p.rd_hd >> 5) - 1 : 0;    // 64 / 128 columns = 2 / 4 chunks
+      const int rd_shift = (p.rd_hd == 128) ? 7 : 6;
+      float* rd_dst = nullptr;
+      if (EPI == B200_EPI_ROWDOT) {
+        const int r = row_ok ? row : 0;
+        const int b = r / p.rd_T, t = r - b * p.rd_T;
+        rd_dst = p.rowdot + (static_cast<size_t>(b) * (p.N >> rd_shift)) * p.rd_T + t;   // + head * T
+      }
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
@@ -420,6 +471,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                 if (EPI == B200_EPI_DGELU) {
                   v[2 * j] *= gelu_erf_grad(f.x);
                   v[2 * j + 1] *= gelu_erf_grad(f.y);
+                } else if (EPI == B200_EPI_ROWDOT) {
+                  dot = fmaf(v[2 * j], f.x, dot);
+                  dot = fmaf(v[2 * j + 1], f.y, dot);
                 } else {   // residual add / accumulate
                   v[2 * j] += f.x;
                   v[2 * j + 1] += f.y;
@@ -430,6 +484,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
             *reinterpret_cast<uint4*>(row0 + sw) = o;
           }
+        }
+        if (EPI == B200_EPI_ROWDOT && ((c + 1) & rd_mask) == 0) {
+          const int col_end = n0 + (c + 1) * 32;             // first column after this head
+          if (row_ok && col_end <= p.N) rd_dst[static_cast<size_t>((col_end >> rd_shift) - 1) * p.rd_T] = dot;
+          dot = 0.f;
         }
         if (c & 1) {
           fence_proxy_async();     // generic-proxy smem writes -> visible to the TMA engine
@@ -453,9 +512,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       }
     };
 
-    for (int tile = unit; tile < num_tiles; tile += num_units) {
-      const int m0 = (tile % p.num_m_tiles) * (GEMM_BM * CTAS) + static_cast<int>(cta_rank) * GEMM_BM;
-      const int n0 = (tile / p.num_m_tiles) * BN;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int m0 = (tile % p.num_m_tiles) * (GEMM_BM * CL) + static_cast<int>(crank) * GEMM_BM;
+      const int nt = tile / p.num_m_tiles;
+      const int n0 = nt * BN;
       float* bias_s = s_bias + (tile_no & 1) * BN;
       ++tile_no;
       if (p.epi == B200_EPI_BIAS || p.epi == B200_EPI_BIAS_GELU || p.epi == B200_EPI_BIAS_RESID) {
@@ -472,7 +532,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         case B200_EPI_BIAS_RESID: run_tile(std::integral_constant<int, B200_EPI_BIAS_RESID>{}, m0, n0, bias_s); break;
         case B200_EPI_DGELU: run_tile(std::integral_constant<int, B200_EPI_DGELU>{}, m0, n0, bias_s); break;
         case B200_EPI_ACCUM: run_tile(std::integral_constant<int, B200_EPI_ACCUM>{}, m0, n0, bias_s); break;
+        case B200_EPI_ROWDOT: run_tile(std::integral_constant<int, B200_EPI_ROWDOT>{}, m0, n0, bias_s); break;
         default: run_tile(std::integral_constant<int, B200_EPI_NONE>{}, m0, n0, bias_s); break;
+      }
+      if (bias_grad && nt == 0) {
+        // row sums of A (= the bias gradient): any of the 16 identical columns of the row-sum accumulator
+        uint32_t rs;
+        tmem_ld_32x32b_x1(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + Cfg::kBiasCol, rs);
+        tmem_ld_wait();
+        const int row = m0 + quarter * 32 + lane;
+        if (row < p.M) {
+          float s = __uint_as_float(rs);
+          if (p.dbias_accum) s += __bfloat162float(p.dbias[row]);
+          p.dbias[row] = __float2bfloat16(s);
+        }
       }
       // all tcgen05.ld of this warp are complete (wait::ld above): release the accumulator
       tc_fence_before();
@@ -480,7 +553,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       if (lane == 0) {
         if (CTAS == 2) mbar_arrive_leader(&tempty_bar[acc]); else mbar_arrive(&tempty_bar[acc]);
       }
-      if (++acc == 2) {
+      if (++acc == nacc) {
         acc = 0;
         acc_phase ^= 1;
       }
@@ -490,7 +563,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
 
   tc_fence_before();
   __syncthreads();
-  if (CTAS == 2) cluster_sync_all();   // neither CTA leaves (or frees TMEM) while the pair may still touch it
+  if (CL > 1) cluster_sync_all();   // no CTA leaves (or frees TMEM) while a cluster peer may still touch it
   if (warp == 1) {
     tc_fence_after();
     if (CTAS == 2) tmem_dealloc_2cta(tmem_base, Cfg::kTmemCols); else tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -520,10 +593,45 @@ static PFN_encodeTiled get_encode_fn() {
   return fn;
 }
 
+// Tensor maps depend only on (address, shape, leading dimension, box): the engine calls the same GEMMs on the
+// same buffers every step, so encoded maps are kept in a small direct-mapped cache instead of paying four
+// driver calls per launch (eager mode, the phase profiler and the tests do not replay a CUDA graph).
+struct TmapKey {
+  const void* ptr;
+  uint64_t rows, cols, ld;
+  uint32_t box_rows, box_cols;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows &&
+           box_cols == o.box_cols;
+  }
+};
+struct TmapSlot {
+  TmapKey key;
+  bool valid;
+  CUtensorMap map;
+};
+constexpr int kTmapCacheSlots = 2048;
+static TmapSlot g_tmap_cache[kTmapCacheSlots];
+static std::mutex g_tmap_mutex;
+static unsigned long long g_tmap_hits = 0, g_tmap_misses = 0;
+
 // 2-D bf16 tensor map over a row-major [rows, cols] matrix with leading dimension ld (elements),
 // box = [box_rows, box_cols], 128-byte swizzle (box_cols * 2 bytes must be <= 128).
 int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
                       uint32_t box_rows, uint32_t box_cols) {
+  const TmapKey key{ptr, rows, cols, ld, box_rows, box_cols};
+  uint64_t h = reinterpret_cast<uint64_t>(ptr) * 0x9E3779B97F4A7C15ull;
+  h ^= (rows * 0xC2B2AE3D27D4EB4Full) ^ (cols << 17) ^ (ld << 31) ^ (static_cast<uint64_t>(box_rows) << 7) ^ box_cols;
+  h ^= h >> 29;
+  TmapSlot& slot = g_tmap_cache[h % kTmapCacheSlots];
+  {
+    std::lock_guard<std::mutex> lock(g_tmap_mutex);
+    if (slot.valid && slot.key == key) {
+      memcpy(map, &slot.map, sizeof(CUtensorMap));
+      ++g_tmap_hits;
+      return 0;
+    }
+  }
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) return -1;
   cuuint64_t gdim[2] = {cols, rows};
@@ -533,7 +641,13 @@ int make_tmap_2d_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : -static_cast<int>(r) - 1000;
+  if (r != CUDA_SUCCESS) return -static_cast<int>(r) - 1000;
+  std::lock_guard<std::mutex> lock(g_tmap_mutex);
+  slot.key = key;
+  memcpy(&slot.map, map, sizeof(CUtensorMap));
+  slot.valid = true;
+  ++g_tmap_misses;
+  return 0;
 }
 
 int device_sm_count() {
@@ -545,39 +659,103 @@ int device_sm_count() {
   return sms[dev];
 }
 
-static int g_gemm_pdl = 1;   // b200_set_option("gemm_pdl", 0) turns programmatic dependent launch off
+static int g_gemm_pdl = 1;   // b200_set_gemm_pdl(0) turns programmatic dependent launch off
 
 template <int BN, int CTAS>
-static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md,
-                       const CUtensorMap& md2, GemmParams& p, int max_ctas, cudaStream_t stream) {
+static cudaError_t gemm_func_attrs() {
   using Cfg = GemmCfg<BN, CTAS>;
   static bool attr_done[64] = {false};   // one flag set per template instantiation
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_done[dev & 63]) {
     cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, CTAS>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg::kSmemBytes);
-    if (e != cudaSuccess) return static_cast<int>(e);
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    if (e != cudaSuccess) return e;
     attr_done[dev & 63] = true;
   }
-  p.num_m_tiles = (p.M + GEMM_BM * CTAS - 1) / (GEMM_BM * CTAS);
+  return cudaSuccess;
+}
+
+// Clusters of more than 8 CTAs (8 CTA pairs sharing one B tile) are "non-portable": opt in the first time one
+// is asked for, so that ordinary launches keep the default scheduling.
+template <int BN, int CTAS>
+static cudaError_t gemm_allow_big_clusters() {
+  static bool done[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!done[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, CTAS>,
+                                         cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
+    done[dev & 63] = true;
+  }
+  return cudaSuccess;
+}
+
+// How many clusters of (units * CTAS) CTAs of this kernel can be resident at once (one CTA per SM, every CTA
+// of a cluster inside one GPC).  Cached per device and configuration.
+template <int BN, int CTAS>
+static int max_resident_clusters(int units) {
+  using Cfg = GemmCfg<BN, CTAS>;
+  static int cache[64][GEMM_MAX_UNITS + 1] = {{0}};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (units < 1 || units > GEMM_MAX_UNITS) return 0;
+  if (cache[dev][units]) return cache[dev][units] < 0 ? 0 : cache[dev][units];
+  if (gemm_func_attrs<BN, CTAS>() != cudaSuccess) return 0;
+  if (units * CTAS > 8 && gemm_allow_big_clusters<BN, CTAS>() != cudaSuccess) return 0;
+  int n = 0;
+  if (units == 1) {
+    n = device_sm_count() / CTAS;
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(units * CTAS * 8);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = units * CTAS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_bf16_tcgen05_kernel<BN, CTAS>, &cfg) != cudaSuccess) {
+      cudaGetLastError();
+      n = 0;
+    }
+  }
+  cache[dev][units] = n > 0 ? n : -1;
+  return n;
+}
+
+static int max_resident_clusters_rt(int BN, int CTAS, int units) {
+  if (CTAS == 2) return BN == 256 ? max_resident_clusters<256, 2>(units) : max_resident_clusters<128, 2>(units);
+  return BN == 256 ? max_resident_clusters<256, 1>(units) : max_resident_clusters<128, 1>(units);
+}
+
+template <int BN, int CTAS>
+static int launch_gemm(const CUtensorMap& ma, const BMaps& mb, const CUtensorMap& md,
+                       const CUtensorMap& md2, GemmParams& p, int max_ctas, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN, CTAS>;
+  cudaError_t e = gemm_func_attrs<BN, CTAS>();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  const int CL = p.units * CTAS;
+  p.num_m_tiles = (p.M + GEMM_BM * CL - 1) / (GEMM_BM * CL);
   p.num_n_tiles = (p.N + BN - 1) / BN;
   const int tiles = p.num_m_tiles * p.num_n_tiles;
-  int grid = device_sm_count();
-  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (tiles * CTAS < grid) grid = tiles * CTAS;
-  grid -= grid % CTAS;
-  if (grid < CTAS) grid = CTAS;
-  const int threads = GEMM_THREADS + (p.gather_ws > 0 ? GEMM_GATHER_THREADS : 0);
+  int clusters = max_resident_clusters<BN, CTAS>(p.units);
+  if (clusters < 1) return -9;
+  if (max_ctas > 0 && max_ctas / CL < clusters) clusters = max_ctas / CL > 0 ? max_ctas / CL : 1;
+  if (tiles < clusters) clusters = tiles;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(threads);
+  cfg.gridDim = dim3(clusters * CL);
+  cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // PDL: see pdl_wait() in the kernel
@@ -591,67 +769,104 @@ static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
 
 using namespace b200;
 
-struct GatherArgs {
-  int ws = 0;
-  const void* const* shard_adj = nullptr;
-  unsigned long long flat_off = 0, shard = 0;
-  int rows = 0, cols = 0;
-  void* flags = nullptr;
-  void* epoch = nullptr;
-  int self_gather = 1;
-  unsigned long long pf_flat_off = 0;
-  int pf_rows = 0, pf_cols = 0;
-  void* pf_dst = nullptr;
-  void* pf_flags = nullptr;
-};
-
-__global__ void gather_epoch_bump_kernel(uint32_t* w) { *w += 1; }
-
 static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K, int lda, int ldb,
                      int ldd, int a_mn, int b_mn, int epi, const void* bias, const void* aux,
                      void* D2, float drop_p, unsigned int drop_seed, int bn_hint, int max_ctas,
-                     void* stream, const GatherArgs& ga) {
+                     void* stream, const B200GemmEx* ex) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if ((N % 8) || (K % 8) || (lda % 8) || (ldb % 8) || (ldd % 8)) return -2;
   if (a_mn && (M % 8)) return -2;
+  const int b_ws = (ex && ex->b_ws > 1) ? ex->b_ws : 1;
+  uint32_t b_row0 = 0, b_rpo = 0;
+  if (b_ws > 1) {
+    // the owners' shards are viewed as [rows_per_owner, ldb] matrices: offset and shard size must be whole rows
+    if (b_ws > GEMM_MAX_OWNERS || !ex->b_shards || ex->b_shard_elems == 0 || (ex->b_shard_elems % ldb) ||
+        (ex->b_flat_off % ldb))
+      return -2;
+    b_row0 = static_cast<uint32_t>(ex->b_flat_off / ldb);
+    b_rpo = static_cast<uint32_t>(ex->b_shard_elems / ldb);
+  }
+  const int b_rows = b_mn ? K : N;      // rows of the stored weight matrix
   // bn_hint: 0 = auto, 128 / 256 = single-CTA tile width, 2128 / 2256 = CTA-pair (cta_group::2) mode
   int BN = bn_hint % 1000, CTAS = bn_hint >= 2000 ? 2 : 1;
+  int want_units = ex ? ex->mc_units : 0;   // 0 = auto: multicast only when B comes from peers
+  // Units per cluster for a (bn, ctas) candidate: as many consecutive M-tiles as there are (<= 8, power of two),
+  // every TMA box of B a multiple of 8 rows, and no box may straddle two owners.
+  auto units_for = [&](int bn, int ctas) {
+    int want = want_units > 0 ? want_units : (b_ws > 1 ? GEMM_MAX_UNITS : 1);
+    int u = 1;
+    while (u * 2 <= want && u * 2 <= GEMM_MAX_UNITS && u * 2 * 128 * ctas <= ((M + 127) / 128) * 128) u *= 2;
+    for (; u >= 1; u >>= 1) {
+      const int box = b_mn ? GEMM_BK / u : (bn / ctas) / u;
+      if (box < 8 || (box % 8)) continue;
+      if (b_ws > 1 && ((b_row0 % box) || (b_rpo % box))) continue;
+      if (u > 1 && max_resident_clusters_rt(bn, ctas, u) < 1) continue;
+      return u;
+    }
+    return 0;
+  };
+  int units = 1;
   if (BN != 128 && BN != 256) {
     // Pick (pair mode, tile width) by a wave model: rounds of tiles over the scheduling units times the
     // per-tile main-loop time, with the shared-memory-bandwidth efficiency of each shape
     // (128x128: operand reads + TMA fills = 2 x 128 B/clk -> ~0.5; 128x256 and pair 256x128: ~0.68;
-    //  pair 256x256: ~0.95 — see profiles/README.md).
-    const int sms = device_sm_count();
+    //  pair 256x256: ~0.95 - see profiles/README.md).
     struct Cand { int bn, ctas; double eff; };
     const Cand cands[4] = {{128, 1, 0.50}, {256, 1, 0.68}, {128, 2, 0.68}, {256, 2, 0.95}};
     double best = 1e30;
+    BN = 0;
     for (const Cand& c : cands) {
       if (c.bn > 128 && N < 256) continue;
       if (c.ctas == 2 && M <= 128) continue;
-      const long mt = (M + 128 * c.ctas - 1) / (128 * c.ctas);
+      const int u = units_for(c.bn, c.ctas);
+      if (u < 1) continue;
+      const long mt = (M + 128 * c.ctas * u - 1) / (128 * c.ctas * u);
       const long nt = (N + c.bn - 1) / c.bn;
-      const long units = sms / c.ctas;
-      const long rounds = (mt * nt + units - 1) / units;
-      const double cost = rounds * (c.bn / 128.0) / c.eff + 0.15 * rounds;   // + per-tile epilogue/issue overhead
+      const long slots = max_resident_clusters_rt(c.bn, c.ctas, u);
+      if (slots < 1) continue;
+      const long rounds = (mt * nt + slots - 1) / slots;
+      double cost = rounds * (c.bn / 128.0) / c.eff + 0.15 * rounds;   // + per-tile epilogue/issue overhead
+      // remote B: every unit of M that is NOT covered by the cluster fetches the weight over NVLink again
+      if (b_ws > 1) cost *= 1.0 + 0.25 * (mt - 1);
       if (cost < best - 1e-9) {
         best = cost;
         BN = c.bn;
         CTAS = c.ctas;
+        units = u;
       }
     }
+    if (!BN) return -9;
+  } else {
+    units = units_for(BN, CTAS);
+    if (units < 1) return -9;
   }
-  CUtensorMap ma, mb;
+  const int b_box_rows = b_mn ? GEMM_BK / units : (BN / CTAS) / units;
+  if (b_ws > 1 && ((b_row0 % b_box_rows) || (b_rpo % b_box_rows))) return -9;
+  (void)b_rows;
+
+  CUtensorMap ma;
+  BMaps mb;
   int rc;
   if (!a_mn)
     rc = make_tmap_2d_bf16(&ma, A, M, K, lda, GEMM_BM, 64);
   else
     rc = make_tmap_2d_bf16(&ma, A, K, M, lda, GEMM_BK, 64);
   if (rc) return rc;
-  if (!b_mn)
-    rc = make_tmap_2d_bf16(&mb, B, N, K, ldb, BN / CTAS, 64);
-  else
-    rc = make_tmap_2d_bf16(&mb, B, K, N, ldb, GEMM_BK, 64);
-  if (rc) return rc;
+  if (b_ws > 1) {
+    // one map per owner over its whole shard [rows_per_owner, ldb]; the kernel picks the owner per box
+    for (int o = 0; o < b_ws; ++o) {
+      rc = make_tmap_2d_bf16(&mb.m[o], ex->b_shards[o], b_rpo, ldb, ldb, b_box_rows, 64);
+      if (rc) return rc;
+    }
+    for (int o = b_ws; o < GEMM_MAX_OWNERS; ++o) mb.m[o] = mb.m[0];
+  } else {
+    if (!b_mn)
+      rc = make_tmap_2d_bf16(&mb.m[0], B, N, K, ldb, b_box_rows, 64);
+    else
+      rc = make_tmap_2d_bf16(&mb.m[0], B, K, N, ldb, b_box_rows, 64);
+    if (rc) return rc;
+    for (int o = 1; o < GEMM_MAX_OWNERS; ++o) mb.m[o] = mb.m[0];
+  }
   // outputs: 32-row x 64-column boxes, one per epilogue warp and 64-column chunk
   CUtensorMap md, md2;
   rc = make_tmap_2d_bf16(&md, D, M, N, ldd, 32, 64);
@@ -660,6 +875,7 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   if (rc) return rc;
 
   GemmParams p;
+  memset(&p, 0, sizeof(p));
   p.M = M;
   p.N = N;
   p.K = K;
@@ -680,42 +896,37 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   }
   p.drop_seed = drop_seed;
   p.seed_ptr = step_seed_ptr();
-  p.gather_ws = ga.ws;
-  if (ga.ws > 0) {
-    if (ga.ws > 8 || ldb != ga.cols || (ga.cols % 8) || (ga.flat_off % 8) || (ga.shard % 8)) return -2;
-    p.g_rows = ga.rows;
-    p.g_cols = ga.cols;
-    p.g_chunk_rows = 32;   // small chunks: every CTA's gather warps get work, flags stay fine-grained
-    p.g_flat_off = ga.flat_off;
-    p.g_shard = ga.shard;
-    for (int r = 0; r < 8; ++r)
-      p.g_src[r] = r < ga.ws ? static_cast<const __nv_bfloat16*>(ga.shard_adj[r]) : nullptr;
-    p.g_dst = static_cast<__nv_bfloat16*>(const_cast<void*>(B));
-    p.g_flags = static_cast<uint32_t*>(ga.flags);
-    p.g_epoch = static_cast<const uint32_t*>(ga.epoch);
-    p.g_self = ga.self_gather;
-    p.pf_rows = ga.pf_rows;
-    p.pf_cols = ga.pf_cols;
-    p.pf_flat_off = ga.pf_flat_off;
-    p.pf_dst = static_cast<__nv_bfloat16*>(ga.pf_dst);
-    p.pf_flags = static_cast<uint32_t*>(ga.pf_flags);
-    if (ga.pf_rows > 0 && ((ga.pf_cols % 8) || (ga.pf_flat_off % 8) || (ga.pf_rows + 31) / 32 > 1024)) return -2;
+  p.units = units;
+  p.b_ws = b_ws;
+  p.b_row0 = b_row0;
+  p.b_rows_per_owner = b_rpo ? b_rpo : 1;
+  if (ex) {
+    p.dbias = static_cast<__nv_bfloat16*>(ex->dbias);
+    p.dbias_accum = ex->dbias_accum;
+    p.rowdot = ex->rowdot;
+    p.rd_T = ex->rd_T;
+    p.rd_hd = ex->rd_hd;
   }
+  if (epi == B200_EPI_ROWDOT) {
+    if (!p.rowdot || !p.aux || p.rd_T <= 0 || (p.rd_hd != 64 && p.rd_hd != 128) || (N % p.rd_hd) || (M % p.rd_T))
+      return -2;
+  }
+  if (p.dbias && epi != B200_EPI_NONE && epi != B200_EPI_ACCUM) return -2;   // the ones tile uses the bias slice
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  int rc2;
   if (CTAS == 2)
-    rc2 = (BN == 256) ? launch_gemm<256, 2>(ma, mb, md, md2, p, max_ctas, s) : launch_gemm<128, 2>(ma, mb, md, md2, p, max_ctas, s);
-  else
-    rc2 = (BN == 256) ? launch_gemm<256, 1>(ma, mb, md, md2, p, max_ctas, s) : launch_gemm<128, 1>(ma, mb, md, md2, p, max_ctas, s);
-  if (rc2 == 0 && ga.ws > 0) {
-    gather_epoch_bump_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(ga.epoch));
-    rc2 = static_cast<int>(cudaGetLastError());
-  }
-  return rc2;
+    return (BN == 256) ? launch_gemm<256, 2>(ma, mb, md, md2, p, max_ctas, s) : launch_gemm<128, 2>(ma, mb, md, md2, p, max_ctas, s);
+  return (BN == 256) ? launch_gemm<256, 1>(ma, mb, md, md2, p, max_ctas, s) : launch_gemm<128, 1>(ma, mb, md, md2, p, max_ctas, s);
 }
 
 extern "C" int b200_set_gemm_pdl(int on) {
   g_gemm_pdl = on ? 1 : 0;
+  return 0;
+}
+
+extern "C" int b200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses) {
+  std::lock_guard<std::mutex> lock(g_tmap_mutex);
+  if (hits) *hits = g_tmap_hits;
+  if (misses) *misses = g_tmap_misses;
   return 0;
 }
 
@@ -724,37 +935,13 @@ extern "C" int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int 
                               const void* aux, void* D2, float drop_p, unsigned int drop_seed,
                               int bn_hint, int max_ctas, void* stream) {
   return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, epi, bias, aux, D2, drop_p, drop_seed,
-                   bn_hint, max_ctas, stream, GatherArgs());
+                   bn_hint, max_ctas, stream, nullptr);
 }
 
-// K14: same GEMM, but B (a weight matrix of `rows` x `cols`, partitioned over `ws` ranks by flat
-// offset) is first pulled from the owners' shards into `B_staging` by extra warps of the SAME kernel,
-// chunk by chunk, while the tensor cores already work on the chunks that have arrived.
-extern "C" int b200_gemm_bf16_gather(const void* A, void* B_staging, void* D, int M, int N, int K,
-                                     int lda, int ldb, int ldd, int a_mn, int b_mn, int epi,
-                                     const void* bias, const void* aux, void* D2, float drop_p,
-                                     unsigned int drop_seed, int bn_hint, int max_ctas, void* stream,
-                                     const void* const* shard_adj, int ws,
-                                     unsigned long long flat_off, unsigned long long shard_elems,
-                                     int rows, int cols, void* chunk_flags, void* epoch_word,
-                                     int self_gather, unsigned long long pf_flat_off, int pf_rows,
-                                     int pf_cols, void* pf_staging, void* pf_flags) {
-  GatherArgs ga;
-  ga.self_gather = self_gather;
-  ga.pf_flat_off = pf_flat_off;
-  ga.pf_rows = pf_rows;
-  ga.pf_cols = pf_cols;
-  ga.pf_dst = pf_staging;
-  ga.pf_flags = pf_flags;
-  ga.ws = ws;
-  ga.shard_adj = shard_adj;
-  ga.flat_off = flat_off;
-  ga.shard = shard_elems;
-  ga.rows = rows;
-  ga.cols = cols;
-  ga.flags = chunk_flags;
-  ga.epoch = epoch_word;
-  if ((rows + 31) / 32 > 1024) return -3;   // chunk_flags holds 1024 words
-  return gemm_impl(A, B_staging, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, epi, bias, aux, D2, drop_p,
-                   drop_seed, bn_hint, max_ctas, stream, ga);
+extern "C" int b200_gemm_bf16_ex(const void* A, const void* B, void* D, int M, int N, int K, int lda,
+                                 int ldb, int ldd, int a_mn, int b_mn, int epi, const void* bias,
+                                 const void* aux, void* D2, float drop_p, unsigned int drop_seed,
+                                 int bn_hint, int max_ctas, void* stream, const B200GemmEx* ex) {
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, a_mn, b_mn, epi, bias, aux, D2, drop_p, drop_seed,
+                   bn_hint, max_ctas, stream, ex);
 }

@@ -223,6 +223,33 @@ __device__ __forceinline__ void tma_load_2d_2cta(const CUtensorMap* m, uint64_t*
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
       : "memory");
 }
+// Multicast variants: the box lands at the same CTA-relative offset in every CTA of `mask` (bit i = cluster rank
+// i) and each destination's mbarrier (same offset; for cta_group::2 the even CTA of each destination pair) is
+// credited with the bytes.  One remote tile crosses L2 / NVLink once per cluster instead of once per CTA.
+__device__ __forceinline__ void tma_load_2d_mc(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1,
+                                               uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2cta_mc(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1,
+                                                    uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+// cta_group::1 commit that arrives on the barrier at this offset in every CTA of `mask`.
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
 __device__ __forceinline__ void umma_bf16_ss_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                                   uint32_t accumulate) {
   asm volatile(
@@ -234,12 +261,13 @@ __device__ __forceinline__ void umma_bf16_ss_2cta(uint32_t tmem_d, uint64_t ades
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// Arrive (once all earlier MMAs of this thread retired) on the barrier at this offset in BOTH CTAs.
-__device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
+// Arrive (once all earlier MMAs of this thread retired) on the barrier at this offset in every CTA of `mask`
+// (default: the two CTAs of a pair that is alone in its cluster).
+__device__ __forceinline__ void umma_commit_2cta(uint64_t* bar, uint16_t mask = 3) {
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
           smem_u32(bar)),
-      "h"(static_cast<uint16_t>(3))
+      "h"(mask)
       : "memory");
 }
 // Arrive on the LEADER CTA's copy of a barrier (from either CTA of the pair).
@@ -265,6 +293,9 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
         "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr)
       : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x1(uint32_t taddr, uint32_t& r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(

@@ -24,6 +24,8 @@ extern "C" {
 #define B200_EPI_BIAS_RESID 3 /* D = aux + dropout(acc + bias)       (TH:121-122,128,130) */
 #define B200_EPI_DGELU 4      /* D = acc * gelu_erf'(aux)            (backward of TH:120) */
 #define B200_EPI_ACCUM 5      /* D = D + acc                         (wgrad accumulation) */
+#define B200_EPI_ROWDOT 6     /* D = acc ; rowdot[(b*H+h)*T+t] = sum over head h of acc*aux   (attention-backward
+                                 D = rowsum(dO o O), produced by the out-proj dgrad that writes dO) */
 
 /* D[M,N] = epi(A * B^T), tcgen05/TMEM/TMA.  a_mn / b_mn: 0 = operand stored [rows, K]
  * (K-major), 1 = stored [K, rows] (MN-major).  lda/ldb/ldd in elements, multiples of 8.
@@ -49,12 +51,36 @@ int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const
                        void* dqkv, float* D, float* dq_acc, int B, int T, int H, int head_dim,
                        int causal, float drop_p, unsigned int seed, void* stream);
 
+/* Same, with the two helper passes optional.  flags:
+ *   B200_ATTN_BWD_HAVE_D       D already holds rowsum(dO o O) per (batch, head, query) - e.g. written by the out-proj
+ *                              dgrad GEMM with B200_EPI_ROWDOT - so the preparation kernel is skipped;
+ *   B200_ATTN_BWD_ACC_IS_ZERO  dq_acc is all zeros on entry (every call leaves it zeroed again), so it is not cleared.
+ * With both flags the backward is two launches: the main kernel and the fp32 -> bf16 dQ conversion. */
+#define B200_ATTN_BWD_HAVE_D 1
+#define B200_ATTN_BWD_ACC_IS_ZERO 2
+int b200_attention_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse,
+                          void* dqkv, float* D, float* dq_acc, int B, int T, int H, int head_dim,
+                          int causal, float drop_p, unsigned int seed, void* stream, int flags);
+
 /* ---- LayerNorm (TH:113,117,56) ------------------------------------------------ */
 int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
                        float* rstd, int M, int d, float eps, void* stream);
 /* dx = LayerNorm'(dy) + dres (dres may be NULL) */
 int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
                        const float* rstd, const void* dres, void* dx, int M, int d, void* stream);
+/* LayerNorm backward in one pass over dy and x: dx (+ dres), optionally dx_drop = dropout_mask(drop_seed) * dx /
+ * (1 - drop_p) with the element indexing of the GEMM dropout epilogue (row * d + col), and optionally (partials !=
+ * NULL) per-CTA fp32 partial column sums of dy*xhat and dy, b200_layernorm_bwd_fused_scratch_bytes(M, d) bytes.
+ * b200_layernorm_param_fold turns those partials into dgamma / dbeta (accumulate != 0 adds onto them); it only
+ * feeds the optimizer, so it can run on another stream (after the producer, before the partials are reused).
+ * Both steps sum in a fixed order (no atomics). */
+size_t b200_layernorm_bwd_fused_scratch_bytes(int M, int d);
+int b200_layernorm_bwd_fused(const void* dy, const void* x, const void* gamma, const float* mean,
+                             const float* rstd, const void* dres, void* dx, void* dx_drop, float drop_p,
+                             unsigned int drop_seed, void* partials, size_t partials_bytes, int M, int d,
+                             void* stream);
+int b200_layernorm_param_fold(const void* partials, int M, int d, void* dgamma, void* dbeta, int accumulate,
+                              void* stream);
 /* Scratch needed by the two column reductions below: 256 per-column-block completion
  * counters followed by fp32 partial sums.  The buffer must be zero-filled once before its first use; every call
  * leaves the counters zeroed again.  Calls sharing one scratch buffer must be stream-ordered. */
@@ -72,7 +98,9 @@ int b200_colsum(const void* dy, void* out, int M, int N, int ld, int accumulate,
  * memory, or a loop that must stay clear of cudaMalloc's driver locks and device synchronisation.
  * The scratch is a 512 KiB device array built into the library (held by every GPU that loads it until
  * exit), so no buffer is passed and nothing is allocated or freed.  The FIRST call on each device
- * looks up the array's device address; make it before any stream capture.  All calls on a GPU share
+ * looks up the array's device address; make it before any stream capture.  (The per-device address cache is
+ * written without a lock: two host threads making that first call on one device at the same moment both
+ * store the same value, which is harmless.)  All calls on a GPU share
  * the one array: keep them stream-ordered, overlapping calls race.  Limit: N <= 65536 columns and
  * scratch <= b200_colsum_static_max_bytes(); larger shapes return B200_ERR_STATIC_SCRATCH. */
 #define B200_ERR_STATIC_SCRATCH (-8)
@@ -132,23 +160,37 @@ int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* fl
 /* GEMM launches use programmatic dependent launch (their prologue overlaps the previous kernel's tail;
  * the kernel waits with griddepcontrol.wait before touching global memory).  0 turns it off. */
 int b200_set_gemm_pdl(int on);
-/* K14: the GEMM of b200_gemm_bf16 with the all-gather of its B operand fused in.  B is a weight
- * matrix [rows, cols] partitioned over ws ranks by flat offset (partition size shard_elems, B[0,0] at
- * flat_off); shard_adj[r] = rank r's partition base MINUS r*shard_elems elements, as mapped here.
- * Four extra warps per CTA pull 32-row chunks into B_staging and publish chunk_flags (1024 words,
- * zero-filled once); the TMA producer waits per chunk.  epoch_word: device uint32, zero-filled once.
- * self_gather=0 means an earlier call already prefetched B into B_staging; pf_* (pf_rows=0: none)
- * names the NEXT call's weight, which this kernel pulls into pf_staging / pf_flags while it computes
- * (use two staging buffers and two flag arrays alternately).
- * Replaces FSDP's pre-forward all-gather / ZeRO-3's per-module gathers (TH:231-237,366; SURVEY N4,N8). */
-int b200_gemm_bf16_gather(const void* A, void* B_staging, void* D, int M, int N, int K, int lda,
-                          int ldb, int ldd, int a_mn, int b_mn, int epi, const void* bias,
-                          const void* aux, void* D2, float drop_p, unsigned int drop_seed, int bn_hint,
-                          int max_ctas, void* stream, const void* const* shard_adj, int ws,
-                          unsigned long long flat_off, unsigned long long shard_elems, int rows,
-                          int cols, void* chunk_flags, void* epoch_word, int self_gather,
-                          unsigned long long pf_flat_off, int pf_rows, int pf_cols, void* pf_staging,
-                          void* pf_flags);
+/* Extended GEMM arguments (all optional; a zeroed struct = b200_gemm_bf16).
+ *  dbias / dbias_accum   weight-gradient GEMMs (epi NONE or ACCUM): dbias[m] (+)= sum_k A[m,k], the bias gradient,
+ *                        from a 16-column row-sum MMA against an all-ones tile in the same main loop (replaces a
+ *                        separate column-reduction kernel over dY).
+ *  rowdot, rd_T, rd_hd   for B200_EPI_ROWDOT (rd_hd = 64 or 128 columns per head, M a multiple of rd_T).
+ *  b_shards, b_ws, b_flat_off, b_shard_elems
+ *                        K14: B is a weight matrix that is partitioned over b_ws ranks by flat offset
+ *                        (partition size b_shard_elems, B[0,0] at flat offset b_flat_off; both multiples of ldb).
+ *                        b_shards[r] = base of rank r's partition as mapped in THIS process (peer memory).  The B
+ *                        argument itself is ignored: every B tile is fetched by TMA straight from its owner.
+ *                        Replaces FSDP's pre-forward all-gather / ZeRO-3's per-module gathers (TH:229-237,366;
+ *                        SURVEY N4,N8).  Returns -9 when no tile shape keeps every TMA box inside one owner.
+ *  mc_units              tile units (CTAs / CTA pairs along M) per thread-block cluster that share each B tile by
+ *                        TMA multicast: 0 = auto (off for local B, as many as cover M, <= 8, for partitioned B),
+ *                        1 = off, 2 / 4 / 8 = forced. */
+typedef struct B200GemmEx {
+  void* dbias;
+  int dbias_accum;
+  float* rowdot;
+  int rd_T, rd_hd;
+  const void* const* b_shards;
+  int b_ws;
+  unsigned long long b_flat_off, b_shard_elems;
+  int mc_units;
+} B200GemmEx;
+int b200_gemm_bf16_ex(const void* A, const void* B, void* D, int M, int N, int K, int lda, int ldb,
+                      int ldd, int a_mn, int b_mn, int epi, const void* bias, const void* aux, void* D2,
+                      float drop_p, unsigned int drop_seed, int bn_hint, int max_ctas, void* stream,
+                      const B200GemmEx* ex);
+/* Encoded TMA descriptors are cached by (address, shape, box); counters for tests and diagnostics. */
+int b200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
 /* Plain gather of the flat range [flat_off, flat_off+n) from the owners' partitions into dst. */
 int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst, unsigned long long flat_off,
                            unsigned long long n, unsigned long long shard_elems, int ctas,

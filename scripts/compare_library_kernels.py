@@ -23,7 +23,15 @@ from b200bench.config import get_model_config  # noqa: E402
 BF16 = torch.bfloat16
 
 
-def timed(fn, iters):
+CLOCKS = []          # one record per timed region: (label, sm_mhz, sm_max_mhz, reasons, power)
+_LABEL = ["?"]
+
+
+def timed(fn, iters, min_ms=250.0):
+    """Mean device time per call in us.  The region is stretched to >= min_ms so that the NVML clock sampler
+    (20 ms period) sees it under load; its summary is appended to CLOCKS."""
+    from b200bench.utils.clocks import ClockSampler
+
     for i in range(5):
         fn(i)
     torch.cuda.synchronize()
@@ -33,7 +41,18 @@ def timed(fn, iters):
         fn(i)
     e1.record()
     torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / iters * 1e3            # us
+    probe = e0.elapsed_time(e1) / iters                    # ms per call
+    n = max(iters, int(min_ms / max(probe, 1e-4)))
+    sampler = ClockSampler(0, period=0.02).start()
+    e0.record()
+    for i in range(n):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    c = sampler.stop()
+    CLOCKS.append((_LABEL[0], c.get("sm_mhz"), c.get("sm_max_mhz"), ",".join(c.get("reasons") or []) or "none",
+                   c.get("power_w_max")))
+    return e0.elapsed_time(e1) / n * 1e3            # us
 
 
 def copies(bytes_per_set):
@@ -59,8 +78,10 @@ def main():
     # (name, kind, rows of x, N = out features, K = in features)
     shapes = [("qkv fwd", "fwd", M, 3 * d, d), ("proj fwd", "fwd", M, d, d), ("fc1 fwd", "fwd", M, 4 * d, d),
               ("fc2 fwd", "fwd", M, d, 4 * d), ("lm_head fwd", "fwd", M, V, d),
-              ("qkv dgrad", "dgrad", M, 3 * d, d), ("fc1 dgrad", "dgrad", M, 4 * d, d), ("fc2 dgrad", "dgrad", M, d, 4 * d),
-              ("qkv wgrad", "wgrad", M, 3 * d, d), ("fc1 wgrad", "wgrad", M, 4 * d, d), ("fc2 wgrad", "wgrad", M, d, 4 * d)]
+              ("qkv dgrad", "dgrad", M, 3 * d, d), ("proj dgrad", "dgrad", M, d, d), ("fc1 dgrad", "dgrad", M, 4 * d, d),
+              ("fc2 dgrad", "dgrad", M, d, 4 * d), ("lm_head dgrad", "dgrad", M, V, d),
+              ("qkv wgrad", "wgrad", M, 3 * d, d), ("proj wgrad", "wgrad", M, d, d), ("fc1 wgrad", "wgrad", M, 4 * d, d),
+              ("fc2 wgrad", "wgrad", M, d, 4 * d), ("lm_head wgrad", "wgrad", M, V, d)]
     for name, kind, m, n, k in shapes:
         nset = copies((m * k + n * k + m * n) * 2)
         x = [torch.randn(m, k, device=dev, dtype=BF16) for _ in range(nset)]
@@ -68,6 +89,7 @@ def main():
         y = [torch.randn(m, n, device=dev, dtype=BF16) for _ in range(nset)]
         dx = [torch.empty(m, k, device=dev, dtype=BF16) for _ in range(nset)]
         dw = [torch.empty(n, k, device=dev, dtype=BF16) for _ in range(nset)]
+        _LABEL[0] = name
         if kind == "fwd":
             ours = timed(lambda i: o.linear_fwd(x[i % nset], w[i % nset], y[i % nset]), a.iters)
             lib = timed(lambda i: torch.matmul(x[i % nset], w[i % nset].t(), out=y[i % nset]), a.iters)
@@ -89,6 +111,7 @@ def main():
     dqkv = torch.empty_like(qkv)
     D = torch.empty(B * H * T, device=dev, dtype=torch.float32)
     dq_acc = torch.empty(B * T, d, device=dev, dtype=torch.float32)
+    _LABEL[0] = "attention"
     f_ours = timed(lambda i: o.attention_fwd(qkv, out, lse, B, T, H, hd), a.iters)
     b_ours = timed(lambda i: o.attention_bwd(qkv, out, dout, lse, dqkv, D, dq_acc, B, T, H, hd), a.iters)
     q, k_, v = (t.reshape(B, T, H, hd).transpose(1, 2).contiguous().requires_grad_(True)
@@ -104,6 +127,12 @@ def main():
     print(f"| forward | {f_ours:.1f} | {fl / f_ours / 1e6:.0f} | {f_lib:.1f} | {fl / f_lib / 1e6:.0f} |")
     print(f"| backward (ours) vs forward+backward minus forward (SDPA) | {b_ours:.1f} | {2.5 * fl / b_ours / 1e6:.0f} | "
           f"{fb_lib - f_lib:.1f} | {2.5 * fl / max(1e-3, fb_lib - f_lib) / 1e6:.0f} |")
+    print("\nClock record per timed region (NVML, 20 ms period, sampled while the region ran; two regions per GEMM row: "
+          "ours, then cuBLAS; four for attention):\n")
+    print("| region | sm MHz (median) | sm max MHz | throttle reasons | power W max |")
+    print("|---|---|---|---|---|")
+    for lab, mhz, mx, rs, pw in CLOCKS:
+        print(f"| {lab} | {mhz} | {mx} | {rs} | {pw} |")
 
 
 if __name__ == "__main__":

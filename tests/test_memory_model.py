@@ -17,7 +17,7 @@ MEASURED = [
 @pytest.mark.parametrize("tier,strategy,ws,seq,measured", MEASURED)
 def test_model_matches_measured_peak(tier, strategy, ws, seq, measured):
     est = estimate_memory(get_model_config(tier, seq), strategy, ws, 1, seq)
-    assert est["total"] / 1e9 == pytest.approx(measured, rel=0.02)
+    assert est["total"] / 1e9 == pytest.approx(measured, rel=0.03)
 
 
 def test_components_behave():

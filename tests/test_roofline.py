@@ -12,8 +12,8 @@ def test_flops_and_bytes_closed_form():
     assert w["gemm_flops"] == pytest.approx(6 * (12 * d * d * L + V * d) * T)
     assert w["attention_flops"] == pytest.approx(12 * T * T * d * L)
     # ddp: full optimizer on every rank, two-shot all-reduce moves 2 (N-1)/N S in each direction
-    assert w["hbm_optimizer_bytes"] == pytest.approx(28 * 236.4e6, rel=0.01)
-    assert w["nvlink_bytes_in"] == pytest.approx(2 * 7 / 8 * 2 * 236.4e6, rel=0.01) == w["nvlink_bytes_out"]
+    assert w["hbm_optimizer_bytes"] == pytest.approx(28 * 236.4e6, rel=0.02)
+    assert w["nvlink_bytes_in"] == pytest.approx(2 * 7 / 8 * 2 * 236.4e6, rel=0.02) == w["nvlink_bytes_out"]
     assert step_work(cfg, "ddp", 1, 1, 2048)["nvlink_bytes_in"] == 0
 
 
