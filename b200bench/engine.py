@@ -172,6 +172,9 @@ class NativeEngine:
         # into dgamma / dbeta run on the side stream
         self.ln_part = [torch.empty(self.ops.layernorm_bwd_fused_scratch_bytes(M, d) // 4, dtype=torch.float32,
                                     device=dev) for _ in range(2)]
+        self._ab = set(filter(None, os.environ.get("B200BENCH_AB", "").split(",")))   # A/B switches (diagnostics)
+        sbytes = max(self.ops.colreduce_scratch_bytes(M, 4 * d, 1), self.ops.colreduce_scratch_bytes(M, d, 2))
+        self.scratch_side = torch.zeros(sbytes // 4 + 64, dtype=torch.float32, device=dev)   # counters start at 0
         # weight-gradient GEMMs and bias / LayerNorm-parameter reductions do not feed the backward chain:
         # they run on a side stream and fill the tail bubbles of the dgrad -> attention -> LN kernels
         self.side = torch.cuda.Stream(device=dev)
@@ -344,7 +347,8 @@ class NativeEngine:
                          aux=self.x[l], peer=g)
             o.layernorm_fwd(self.xmid[l], P[pre + "ln_2.weight"], P[pre + "ln_2.bias"], self.ln2[l], st[2], st[3])
             w, g = self._w(pre + "mlp.0.weight")
-            o.linear_fwd(self.ln2[l], w, self.pre[l], bias=P[pre + "mlp.0.bias"], epi=_ops.EPI_BIAS_GELU,
+            # the forward keeps gelu'(pre) instead of pre: the backward epilogue is then a multiply
+            o.linear_fwd(self.ln2[l], w, self.pre[l], bias=P[pre + "mlp.0.bias"], epi=_ops.EPI_BIAS_GELU_GRAD,
                          out2=self.act[l], peer=g)
             w, g = self._w(pre + "mlp.2.weight")
             o.linear_fwd(self.act[l], w, self.x[l + 1], bias=P[pre + "mlp.2.bias"], epi=_ops.EPI_BIAS_RESID,
@@ -352,6 +356,31 @@ class NativeEngine:
         o.layernorm_fwd(self.x[self.L], P["transformer.ln_f.weight"], P["transformer.ln_f.bias"], self.lnf,
                         self.statf[0], self.statf[1])
         o.linear_fwd(self.lnf, P["transformer.wte.weight"], self.logits)
+
+    def _ln_bwd(self, dy, x, gamma, mean, rstd, dx, dres, drop_out, seed, part, dg, db, acc):
+        """LayerNorm backward + parameter gradients (+ dropout-masked copy for the block below)."""
+        o, p = self.ops, self.dropout
+        M, d = x.shape
+        if "oldln" in self._ab:         # diagnostics: round-1 schedule (three kernels)
+            o.layernorm_bwd(dy, x, gamma, mean, rstd, dx, dres=dres)
+            self._on_side(lambda: o.layernorm_bwd_params(dy, x, mean, rstd, dg, db, self.scratch_side, acc))
+            if drop_out is not None:
+                o.dropout_apply(dx, drop_out, M, d, p, seed)
+            return
+        if "lnpart" in self._ab:        # column sums inside the main-stream kernel + fold on the side stream
+            o.layernorm_bwd_fused(dy, x, gamma, mean, rstd, dx, dres=dres, dx_drop=drop_out, drop_p=p, seed=seed,
+                                  partials=part)
+            self._on_side(lambda: self._fold(part, M, d, dg, db, acc))
+            return
+        # Default: the main stream gets the lightest possible kernel (dx + the masked copy: no shared memory, no
+        # block barriers, < 128 registers, so it slots in next to side-stream CTAs); dgamma / dbeta only feed the
+        # optimizer and are reduced on the side stream.  Measured 0.15 ms per step faster than the in-kernel sums.
+        o.layernorm_bwd_fused(dy, x, gamma, mean, rstd, dx, dres=dres, dx_drop=drop_out, drop_p=p, seed=seed)
+        self._on_side(lambda: o.layernorm_bwd_params(dy, x, mean, rstd, dg, db, self.scratch_side, acc))
+
+    def _fold(self, part, M, d, dg, db, acc):
+        if "nofold" not in self._ab:
+            self.ops.layernorm_param_fold(part, M, d, dg, db, acc)
 
     def _on_side(self, fn):
         """Run ``fn`` (kernels that only produce parameter gradients) on the side stream, ordered after
@@ -388,16 +417,21 @@ class NativeEngine:
                         grad_scale=1.0 / self.accum, write_grad=True)
         wte = P["transformer.wte.weight"]
         drop = p > 0
+        if "colsum" in self._ab:        # diagnostics: separate column-sum kernels instead of the row-sum MMA
+            def wgrad(dy_, x_, dw_, accumulate, dbias):
+                o.colsum(dy_, dbias, self.scratch_side, accumulate)
+                o.linear_wgrad(dy_, x_, dw_, accumulate=accumulate)
+        else:
+            def wgrad(dy_, x_, dw_, accumulate, dbias):
+                o.linear_wgrad(dy_, x_, dw_, accumulate=accumulate, dbias=dbias)
         # lm_head: dlnf = dlogits @ wte ; dwte (+)= dlogits^T @ lnf      (tied weight)
         self._on_side(lambda: o.linear_wgrad(self.logits, self.lnf, G["transformer.wte.weight"], accumulate=acc))
         o.linear_dgrad(self.logits, wte, self.dln)
         # every LayerNorm backward is ONE launch: input gradient (+ residual gradient), gamma / beta gradients, and
         # - when the block below ends in a dropout - the masked copy of the gradient that its fc2 GEMMs consume
-        o.layernorm_bwd_fused(self.dln, self.x[self.L], P["transformer.ln_f.weight"], self.statf[0], self.statf[1],
-                              self.dres, dx_drop=self.dy_drop if drop else None, drop_p=p,
-                              seed=self._seed(self.L - 1, 2), partials=self.ln_part[0])
-        self._on_side(lambda: o.layernorm_param_fold(self.ln_part[0], M, d, G["transformer.ln_f.weight"],
-                                                     G["transformer.ln_f.bias"], acc))
+        self._ln_bwd(self.dln, self.x[self.L], P["transformer.ln_f.weight"], self.statf[0], self.statf[1], self.dres,
+                     None, self.dy_drop if drop else None, self._seed(self.L - 1, 2), self.ln_part[0],
+                     G["transformer.ln_f.weight"], G["transformer.ln_f.bias"], acc)
         for l in reversed(range(self.L)):
             pre = f"transformer.h.{l}."
             st = self.stats[l]
@@ -406,38 +440,39 @@ class NativeEngine:
             self._layer_begin(l, -1)
             # ---- MLP ----  (weight-gradient GEMMs also emit the bias gradient: row sums of dY^T in the same loop)
             dy = self.dy_drop if drop else self.dres
-            dy_read = self._on_side(lambda dy=dy: o.linear_wgrad(dy, self.act[l], G[pre + "mlp.2.weight"],
-                                                                 accumulate=acc, dbias=G[pre + "mlp.2.bias"]))
+            dy_read = self._on_side(lambda dy=dy: wgrad(dy, self.act[l], G[pre + "mlp.2.weight"],
+                                                        accumulate=acc, dbias=G[pre + "mlp.2.bias"]))
             w, g = self._w(pre + "mlp.2.weight")
-            o.linear_dgrad(dy, w, self.dbig, epi=_ops.EPI_DGELU, aux=self.pre[l], peer=g)
-            self._on_side(lambda: o.linear_wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc,
-                                                 dbias=G[pre + "mlp.0.bias"]))
+            o.linear_dgrad(dy, w, self.dbig, epi=_ops.EPI_MUL, aux=self.pre[l], peer=g)
+            self._on_side(lambda: wgrad(self.dbig, self.ln2[l], G[pre + "mlp.0.weight"], accumulate=acc,
+                                        dbias=G[pre + "mlp.0.bias"]))
             w, g = self._w(pre + "mlp.0.weight")
             o.linear_dgrad(self.dbig, w, self.dln2, peer=g)
-            o.layernorm_bwd_fused(self.dln2, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid,
-                                  dres=self.dres, partials=self.ln_part[0])
+            self._ln_bwd(self.dln2, self.xmid[l], P[pre + "ln_2.weight"], st[2], st[3], self.dmid, self.dres, None, 0,
+                         self.ln_part[0], G[pre + "ln_2.weight"], G[pre + "ln_2.bias"], acc)
             # ---- attention ----
-            self._on_side(lambda: (o.layernorm_param_fold(self.ln_part[0], M, d, G[pre + "ln_2.weight"],
-                                                          G[pre + "ln_2.bias"], acc),
-                                   o.linear_wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"],
-                                                  accumulate=acc, dbias=G[pre + "attn.out_proj.bias"])))
+            self._on_side(lambda: wgrad(self.dmid, self.att[l], G[pre + "attn.out_proj.weight"],
+                                        accumulate=acc, dbias=G[pre + "attn.out_proj.bias"]))
             w, g = self._w(pre + "attn.out_proj.weight")
             # the out-proj dgrad writes dO and, from the same accumulator tile, D = rowsum(dO o O) per head
-            o.linear_dgrad(self.dmid, w, self.datt, epi=_ops.EPI_ROWDOT, aux=self.att[l], peer=g, rowdot=self.attD,
-                           rd_T=T, rd_hd=hd)
-            o.attention_bwd(self.qkv[l], self.att[l], self.datt, self.lse[l], self.dqkv, self.attD, self.dq_acc,
-                            B, T, H, hd, self.causal, p, self._seed(l, 1), have_d=True, acc_is_zero=True)
-            self._on_side(lambda: o.linear_wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"],
-                                                 accumulate=acc, dbias=G[pre + "attn.in_proj_bias"]))
+            if "attn4" in self._ab:
+                o.linear_dgrad(self.dmid, w, self.datt, peer=g)
+                o.attention_bwd(self.qkv[l], self.att[l], self.datt, self.lse[l], self.dqkv, self.attD, self.dq_acc,
+                                B, T, H, hd, self.causal, p, self._seed(l, 1))
+            else:
+                o.linear_dgrad(self.dmid, w, self.datt, epi=_ops.EPI_ROWDOT, aux=self.att[l], peer=g,
+                               rowdot=self.attD, rd_T=T, rd_hd=hd)
+                o.attention_bwd(self.qkv[l], self.att[l], self.datt, self.lse[l], self.dqkv, self.attD, self.dq_acc,
+                                B, T, H, hd, self.causal, p, self._seed(l, 1), have_d=True, acc_is_zero=True)
+            self._on_side(lambda: wgrad(self.dqkv, self.ln1[l], G[pre + "attn.in_proj_weight"],
+                                        accumulate=acc, dbias=G[pre + "attn.in_proj_bias"]))
             w, g = self._w(pre + "attn.in_proj_weight")
             o.linear_dgrad(self.dqkv, w, self.dln, peer=g)
             if dy_read is not None:      # the fc2 weight gradient on the side stream is still entitled to read dy
                 torch.cuda.current_stream().wait_event(dy_read)
-            o.layernorm_bwd_fused(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres,
-                                  dres=self.dmid, dx_drop=self.dy_drop if (drop and l > 0) else None, drop_p=p,
-                                  seed=self._seed(l - 1, 2), partials=self.ln_part[1])
-            self._on_side(lambda: o.layernorm_param_fold(self.ln_part[1], M, d, G[pre + "ln_1.weight"],
-                                                         G[pre + "ln_1.bias"], acc))
+            self._ln_bwd(self.dln, self.x[l], P[pre + "ln_1.weight"], st[0], st[1], self.dres, self.dmid,
+                         self.dy_drop if (drop and l > 0) else None, self._seed(l - 1, 2), self.ln_part[1],
+                         G[pre + "ln_1.weight"], G[pre + "ln_1.bias"], acc)
             a, b = self.layout.layer_range(l)
             if reduce_now:
                 # K13: this block's matrix gradients are final -> all-reduce them on the comm stream

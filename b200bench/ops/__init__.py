@@ -19,7 +19,7 @@ _ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__
 # B200BENCH_LIB selects another build of the same ABI (e.g. `make debug-comm` -> libb200bench_debug.so)
 LIB_PATH = os.environ.get("B200BENCH_LIB") or os.path.join(_ROOT, "b200bench", "lib", "libb200bench.so")
 
-EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_RESID, EPI_DGELU, EPI_ACCUM, EPI_ROWDOT = range(7)
+EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_RESID, EPI_DGELU, EPI_ACCUM, EPI_ROWDOT, EPI_BIAS_GELU_GRAD, EPI_MUL = range(9)
 ATTN_BWD_HAVE_D, ATTN_BWD_ACC_IS_ZERO = 1, 2
 
 

@@ -871,7 +871,9 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
   return static_cast<int>(cudaGetLastError());
 }
 
-static inline int lnb_rows_per_cta(int d) { return (d <= 1024) ? 16 : 8; }   // two rows per warp while they fit in registers
+// One row per warp: the kernel then needs < 128 registers per thread at d = 1024, so its CTAs fit on an SM next to
+// the CTAs of the memory-bound side-stream kernels (AdamW) instead of waiting for a whole free register file.
+static inline int lnb_rows_per_cta(int d) { (void)d; return 8; }
 extern "C" size_t b200_layernorm_bwd_fused_scratch_bytes(int M, int d) {
   const int rpc = lnb_rows_per_cta(d);
   const size_t ctas = (M + rpc - 1) / rpc;
@@ -917,9 +919,9 @@ extern "C" int b200_layernorm_bwd_fused(const void* dy, const void* x, const voi
     }                                                                                                          \
     launch_pdl(layernorm_bwd_fused_kernel<NVV, RPW>, dim3(ctas), dim3(256), smem, s, p);                       \
   } while (0)
-  if (nv <= 1) LNB_LAUNCH(1, 2);
-  else if (nv <= 2) LNB_LAUNCH(2, 2);
-  else if (nv <= 4) LNB_LAUNCH(4, 2);
+  if (nv <= 1) LNB_LAUNCH(1, 1);
+  else if (nv <= 2) LNB_LAUNCH(2, 1);
+  else if (nv <= 4) LNB_LAUNCH(4, 1);
   else if (nv <= 8) LNB_LAUNCH(8, 1);
   else if (nv <= 16) LNB_LAUNCH(16, 1);
   else return -3;

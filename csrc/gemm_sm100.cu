@@ -38,6 +38,20 @@
 #include "b200_internal.h"
 #include "sm100_ptx.cuh"
 
+// Diagnostic build switch: -DGEMM_LANE0_LOOPS runs the producer / MMA loops in lane 0 only (round-1 style).
+#ifdef GEMM_LANE0_LOOPS
+#define GEMM_LOOP_LANES (lane == 0)
+#define GEMM_ELECT() true
+#define GEMM_SYNCWARP() ((void)0)
+#else
+#define GEMM_LOOP_LANES true
+#define GEMM_ELECT() elect_one()
+#define GEMM_SYNCWARP() __syncwarp()
+#endif
+#ifndef GEMM_LAUNCH_BOUND
+#define GEMM_LAUNCH_BOUND 192
+#endif
+
 namespace b200 {
 
 constexpr int GEMM_BM = 128;
@@ -102,7 +116,7 @@ struct GemmParams {
 //           (operand reads + TMA fills = 2 x 128 B/clk), which caps it near 50 % of the tensor peak.
 // A cluster holds p.units such tile units (consecutive M-tiles of one N-tile).
 template <int BN, int CTAS>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_LAUNCH_BOUND, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                          const __grid_constant__ BMaps maps_b,
                          const __grid_constant__ CUtensorMap map_d,
@@ -176,7 +190,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0) {
     // ================================ TMA producer ================================
     // (the whole warp walks the loop with warp-uniform values; one elected lane issues the copies)
-    {
+    if (GEMM_LOOP_LANES) {
       int stage = 0;
       uint32_t phase = 0;
       // This thread's instruction count per k-block is on the critical path of the whole pipeline (it has to stay
@@ -218,7 +232,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           uint8_t* sa = tiles + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
           const int k0 = kb * GEMM_BK;
-          if (elect_one()) {
+          if (GEMM_ELECT()) {
             // pair mode: all bytes (of both CTAs) are credited to the leader's barrier; only it arrives
             if (is_leader) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
             auto load_a = [&](void* dst, int c0, int c1) {
@@ -241,7 +255,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                 issue_b(mb, sb + c * (GEMM_BK * 128) + b_dst_off, n0 + 64 * c, brow);
             }
           }
-          __syncwarp();
+          GEMM_SYNCWARP();
           if (p.b_mn) {
             brow += GEMM_BK;
             if (remote && brow >= static_cast<int>(p.b_rows_per_owner) && owner + 1 < static_cast<uint32_t>(p.b_ws)) {
@@ -258,7 +272,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (is_leader) {
+    if (is_leader && GEMM_LOOP_LANES) {
       // The whole warp walks the loop (warp-uniform control flow and values, so the compiler keeps descriptors and
       // counters in uniform registers); one elected lane issues.
       // The issue rate of this single thread bounds the whole kernel (four MMAs of 128 tensor-core cycles each per
@@ -297,7 +311,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             tc_fence_after();
             const uint64_t ad = adesc0 + static_cast<uint32_t>(stage) * kStageUnits;
             const uint64_t bd = bdesc0 + static_cast<uint32_t>(stage) * kStageUnits;
-            if (elect_one()) {
+            if (GEMM_ELECT()) {
               if (CTAS == 2) {
                 umma_bf16_ss_2cta(tmem_d, ad, bd, idesc, kb ? 1u : 0u);
                 umma_bf16_ss_2cta(tmem_d, ad + a_k, bd + b_k, idesc, 1u);
@@ -311,7 +325,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
               }
               commit_empty(&empty_bar[stage]);
             }
-            __syncwarp();
+            GEMM_SYNCWARP();
             if (++stage == Cfg::kStages) {
               stage = 0;
               phase ^= 1;
@@ -325,7 +339,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             tc_fence_after();
             const uint64_t ad = adesc0 + static_cast<uint32_t>(stage) * kStageUnits;
             const uint64_t bd = bdesc0 + static_cast<uint32_t>(stage) * kStageUnits;
-            if (elect_one()) {
+            if (GEMM_ELECT()) {
 #pragma unroll
               for (uint32_t k = 0; k < GEMM_BK / 16; ++k) {
                 const uint32_t accf = (kb | k) ? 1u : 0u;
@@ -339,7 +353,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
               }
               commit_empty(&empty_bar[stage]);
             }
-            __syncwarp();
+            GEMM_SYNCWARP();
             if (++stage == Cfg::kStages) {
               stage = 0;
               phase ^= 1;
@@ -347,10 +361,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
           }
         }
         // accumulator complete -> epilogue (of both CTAs)
-        if (elect_one()) {
+        if (GEMM_ELECT()) {
           if (CTAS == 2) umma_commit_2cta(&tfull_bar[acc], mask_unit); else umma_commit(&tfull_bar[acc]);
         }
-        __syncwarp();
+        GEMM_SYNCWARP();
         if (++acc == nacc) {
           acc = 0;
           acc_phase ^= 1;
@@ -377,10 +391,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     uint32_t nst = 0;
     auto run_tile = [&](auto epi_c, int m0, int n0, const float* bias_s) {
       constexpr int EPI = decltype(epi_c)::value;
-      constexpr bool HAS_BIAS = (EPI == B200_EPI_BIAS || EPI == B200_EPI_BIAS_GELU || EPI == B200_EPI_BIAS_RESID);
+      constexpr bool HAS_BIAS = (EPI == B200_EPI_BIAS || EPI == B200_EPI_BIAS_GELU || EPI == B200_EPI_BIAS_RESID ||
+                                 EPI == B200_EPI_BIAS_GELU_GRAD);
       constexpr bool HAS_AUX = (EPI == B200_EPI_BIAS_RESID || EPI == B200_EPI_DGELU || EPI == B200_EPI_ACCUM ||
-                                EPI == B200_EPI_ROWDOT);
-      constexpr bool DUAL = (EPI == B200_EPI_BIAS_GELU);
+                                EPI == B200_EPI_ROWDOT || EPI == B200_EPI_MUL);
+      constexpr bool DUAL = (EPI == B200_EPI_BIAS_GELU || EPI == B200_EPI_BIAS_GELU_GRAD);
       const int row = m0 + quarter * 32 + lane;
       const bool row_ok = row < p.M;
       const size_t row_off = static_cast<size_t>(row_ok ? row : 0) * p.ldd;
@@ -445,14 +460,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
             v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
           }
-          if (DUAL) {   // pre-activation -> D, activation -> D2
+          if (DUAL) {   // pre-activation (or the GELU derivative) -> D, activation -> D2
+            float ga[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float dg;
+              gelu_erf_both(v[j], ga[j], dg);
+              if (EPI == B200_EPI_BIAS_GELU_GRAD) v[j] = dg;
+            }
             o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
             o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
             *reinterpret_cast<uint4*>(row0 + sw) = o;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
-            o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
-            o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+            o.x = pack_bf16x2(ga[0], ga[1]); o.y = pack_bf16x2(ga[2], ga[3]);
+            o.z = pack_bf16x2(ga[4], ga[5]); o.w = pack_bf16x2(ga[6], ga[7]);
             *reinterpret_cast<uint4*>(row1 + sw) = o;
           } else {
             if (EPI == B200_EPI_BIAS_RESID && p.drop_threshold) {
@@ -471,6 +491,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
                 if (EPI == B200_EPI_DGELU) {
                   v[2 * j] *= gelu_erf_grad(f.x);
                   v[2 * j + 1] *= gelu_erf_grad(f.y);
+                } else if (EPI == B200_EPI_MUL) {
+                  v[2 * j] *= f.x;
+                  v[2 * j + 1] *= f.y;
                 } else if (EPI == B200_EPI_ROWDOT) {
                   dot = fmaf(v[2 * j], f.x, dot);
                   dot = fmaf(v[2 * j + 1], f.y, dot);
@@ -518,7 +541,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       const int n0 = nt * BN;
       float* bias_s = s_bias + (tile_no & 1) * BN;
       ++tile_no;
-      if (p.epi == B200_EPI_BIAS || p.epi == B200_EPI_BIAS_GELU || p.epi == B200_EPI_BIAS_RESID) {
+      if (p.epi == B200_EPI_BIAS || p.epi == B200_EPI_BIAS_GELU || p.epi == B200_EPI_BIAS_RESID ||
+          p.epi == B200_EPI_BIAS_GELU_GRAD) {
         // stage this tile's bias slice once (overlaps the main loop still running for this tile)
         for (int i = et; i < BN; i += 128)
           bias_s[i] = (n0 + i < p.N) ? __bfloat162float(p.bias[n0 + i]) : 0.f;
@@ -533,6 +557,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
         case B200_EPI_DGELU: run_tile(std::integral_constant<int, B200_EPI_DGELU>{}, m0, n0, bias_s); break;
         case B200_EPI_ACCUM: run_tile(std::integral_constant<int, B200_EPI_ACCUM>{}, m0, n0, bias_s); break;
         case B200_EPI_ROWDOT: run_tile(std::integral_constant<int, B200_EPI_ROWDOT>{}, m0, n0, bias_s); break;
+        case B200_EPI_BIAS_GELU_GRAD: run_tile(std::integral_constant<int, B200_EPI_BIAS_GELU_GRAD>{}, m0, n0, bias_s); break;
+        case B200_EPI_MUL: run_tile(std::integral_constant<int, B200_EPI_MUL>{}, m0, n0, bias_s); break;
         default: run_tile(std::integral_constant<int, B200_EPI_NONE>{}, m0, n0, bias_s); break;
       }
       if (bias_grad && nt == 0) {

@@ -413,13 +413,36 @@ __device__ __forceinline__ uint32_t drop_colkey(uint32_t seed, uint32_t col_inde
 __device__ __forceinline__ bool drop_keep2d(uint32_t a, uint32_t b, uint32_t thr32) {
   return ((a ^ b) * 0x9E3779B1U) >= thr32;
 }
+// Exact (erf) GELU and its derivative, branch-free and cheap enough for a GEMM epilogue: with z = |x| / sqrt(2),
+//   erf(z) = 1 - (a1 t + a2 t^2 + ... + a5 t^5) * exp(-z^2),   t = 1 / (1 + 0.3275911 z)
+// (Abramowitz & Stegun 7.1.26, |error| < 1.5e-7 - far below bf16 resolution), and exp(-z^2) = exp(-x^2 / 2) is the
+// same exponential the normal density of the derivative needs:  gelu'(x) = Phi(x) + x * phi(x).
+// One MUFU.RCP, one MUFU.EX2 and ~12 FMA-pipe operations for both values.
+__device__ __forceinline__ void gelu_erf_both(float x, float& g, float& dg) {
+  const float ax = fabsf(x);
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.3275911f * 0.70710678118654752f, 1.0f)));
+  float e;                                                           // exp(-x^2 / 2)
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * (-0.5f * 1.4426950408889634f)));
+  float poly = fmaf(t, 1.061405429f, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  poly *= t;
+  const float erf_abs = fmaf(-poly, e, 1.0f);
+  const float cdf = fmaf(copysignf(0.5f, x), erf_abs, 0.5f);         // Phi(x) = 0.5 + 0.5 * erf(x / sqrt 2)
+  g = x * cdf;
+  dg = fmaf(x * e, 0.39894228040143268f, cdf);
+}
 __device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+  float g, dg;
+  gelu_erf_both(x, g, dg);
+  return g;
 }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+  float g, dg;
+  gelu_erf_both(x, g, dg);
+  return dg;
 }
 
 }  // namespace b200

@@ -24,6 +24,10 @@ extern "C" {
 #define B200_EPI_BIAS_RESID 3 /* D = aux + dropout(acc + bias)       (TH:121-122,128,130) */
 #define B200_EPI_DGELU 4      /* D = acc * gelu_erf'(aux)            (backward of TH:120) */
 #define B200_EPI_ACCUM 5      /* D = D + acc                         (wgrad accumulation) */
+#define B200_EPI_BIAS_GELU_GRAD 7 /* D = gelu_erf'(acc + bias) ; D2 = gelu_erf(acc + bias): the forward saves the
+                                     derivative instead of the pre-activation, so that the backward epilogue
+                                     (B200_EPI_MUL) is one multiply instead of an erf and an exp per element */
+#define B200_EPI_MUL 8        /* D = acc * aux                       (backward of TH:120 with the saved derivative) */
 #define B200_EPI_ROWDOT 6     /* D = acc ; rowdot[(b*H+h)*T+t] = sum over head h of acc*aux   (attention-backward
                                  D = rowsum(dO o O), produced by the out-proj dgrad that writes dO) */
 
