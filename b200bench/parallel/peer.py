@@ -8,12 +8,18 @@ DDP / FSDP / DeepSpeed do internally (``benchmarking/train_harness.py:186-204,21
 every peer's gradient buffer, weight buffer and flag words, and the collectives are single kernels
 that read and write those pointers over NVLink (K13 all-reduce+scale, K15 reduce-scatter+AdamW+push).
 
-Buffers are allocated with ``cudaMalloc`` inside the native library (IPC cannot export PyTorch's
-caching-allocator blocks) and wrapped as torch tensors without a copy.
+Allocation: first choice is torch's symmetric memory (``cuMemCreate`` + POSIX file-descriptor
+exchange + an NVSwitch multicast object bound to every rank's copy, ``torch.distributed._symmetric_memory``), which
+gives the peer pointers AND a multicast address per buffer - the address the NVLS kernels (``multimem.ld_reduce`` /
+``multimem.st``) work on.  If that is not available (no multicast support, a container without the needed
+syscalls, ``B200BENCH_SYMM_MEM=0``) buffers come from ``cudaMalloc`` inside the native library and are exchanged as
+CUDA IPC handles; there is then no multicast address and the collectives use plain peer loads / stores.
 """
 from __future__ import annotations
 
 import ctypes
+import os
+import sys
 from ctypes import c_float, c_int, c_size_t, c_void_p
 from typing import Dict, List, Optional
 
@@ -32,9 +38,12 @@ class _RawCuda:
 
 
 class PeerBuffer:
-    def __init__(self, name: str, local_ptr: int, nbytes: int, peer_ptrs: List[int], tensor: torch.Tensor):
+    def __init__(self, name: str, local_ptr: int, nbytes: int, peer_ptrs: List[int], tensor: torch.Tensor,
+                 mc_ptr: int = 0, handle=None):
         self.name, self.local_ptr, self.nbytes, self.peer_ptrs, self.tensor = name, local_ptr, nbytes, peer_ptrs, tensor
         self.table = (c_void_p * len(peer_ptrs))(*peer_ptrs)      # host array of device pointers
+        self.mc_ptr = int(mc_ptr or 0)        # multicast (NVLS) address of the buffer, 0 = none
+        self.handle = handle                  # symmetric-memory handle (keeps the mapping alive), None = CUDA IPC
 
 
 class PeerComm:
@@ -56,10 +65,14 @@ class PeerComm:
         L.b200_comm_allreduce.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
         L.b200_comm_rs_adamw.argtypes = [vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
         L.b200_comm_gather_range.argtypes = [vp, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_ulonglong, i, vp]
-        L.b200_comm_push_ranges.argtypes = [vp, vp, i, i, vp, i, vp]
+        L.b200_comm_allreduce_nvls.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
+        L.b200_comm_rs_adamw_nvls.argtypes = [vp, vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
         L.b200_peer_copy.argtypes = [vp, vp, sz, i, vp]
         self.buffers: Dict[str, PeerBuffer] = {}
         self.comm_ctas = comm_ctas
+        self.use_symm = os.environ.get("B200BENCH_SYMM_MEM", "1") != "0"
+        self.use_nvls = os.environ.get("B200BENCH_NVLS", "1") != "0"
+        self.nvls_ctas = int(os.environ.get("B200BENCH_NVLS_CTAS", "0")) or 8
         self.flags = self.alloc("flags", int(L.b200_comm_flag_bytes()), torch.uint8)
         self.stream = torch.cuda.Stream(device=device)
         self._ev_ready = torch.cuda.Event()
@@ -72,6 +85,10 @@ class PeerComm:
         """Every rank must call this with the same arguments, in the same order."""
         nbytes = numel * torch.empty((), dtype=dtype).element_size()
         nbytes = (nbytes + 255) // 256 * 256
+        if self.use_symm:
+            pb = self._alloc_symm(name, numel, nbytes, dtype)
+            if pb is not None:
+                return pb
         ptr = c_void_p()
         handle = (ctypes.c_ubyte * 64)()
         rc = self.ops.lib.b200_peer_alloc(nbytes, ctypes.byref(ptr), ctypes.cast(handle, c_void_p))
@@ -97,6 +114,44 @@ class PeerComm:
         dist.barrier()
         return pb
 
+    def _alloc_symm(self, name: str, numel: int, nbytes: int, dtype: torch.dtype) -> Optional[PeerBuffer]:
+        """Symmetric-memory allocation; every rank must agree on success, so the outcome is all-reduced."""
+        ok, t, hdl = 1, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            t = symm_mem.empty(nbytes, dtype=torch.uint8, device=self.device)
+            try:
+                hdl = symm_mem.rendezvous(t, dist.group.WORLD.group_name)
+            except TypeError:
+                hdl = symm_mem.rendezvous(t, group=dist.group.WORLD)
+            t.zero_()
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            if len(ptrs) != self.ws or ptrs[self.rank] != t.data_ptr():
+                ok = 0
+        except Exception as e:      # noqa: BLE001 - any failure means "use the IPC path"
+            ok = 0
+            if self.rank == 0 and not getattr(self, "_symm_warned", False):
+                print(f"[b200bench] symmetric memory unavailable ({type(e).__name__}: {str(e)[:160]}); "
+                      f"falling back to cudaMalloc + CUDA IPC (no NVLS)", file=sys.stderr, flush=True)
+                self._symm_warned = True
+        flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            self.use_symm = False
+            return None
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        pb = PeerBuffer(name, t.data_ptr(), nbytes, ptrs, t.view(dtype)[:numel], mc_ptr=mc, handle=(hdl, t))
+        self.buffers[name] = pb
+        self.bytes_allocated = getattr(self, "bytes_allocated", 0) + nbytes
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+        return pb
+
+    @property
+    def has_multicast(self) -> bool:
+        return all(pb.mc_ptr != 0 for pb in self.buffers.values()) and len(self.buffers) > 0
+
     # ---- stream plumbing: comm kernels run on a side stream, forked from / joined to compute ------
     def fork(self) -> None:
         """Make the comm stream wait for everything issued so far on the current stream."""
@@ -113,8 +168,12 @@ class PeerComm:
     # ---- collectives -------------------------------------------------------------------------------
     def allreduce(self, buf: PeerBuffer, off: int, n: int, scale: float, side_stream: bool = True) -> None:
         s = self.stream if side_stream else torch.cuda.current_stream()
-        rc = self.ops.lib.b200_comm_allreduce(buf.table, self.flags.table, self.rank, self.ws, off, n, scale,
-                                              self.comm_ctas, c_void_p(s.cuda_stream))
+        if self.use_nvls and buf.mc_ptr:
+            rc = self.ops.lib.b200_comm_allreduce_nvls(c_void_p(buf.mc_ptr), self.flags.table, self.rank, self.ws,
+                                                       off, n, scale, self.nvls_ctas, c_void_p(s.cuda_stream))
+        else:
+            rc = self.ops.lib.b200_comm_allreduce(buf.table, self.flags.table, self.rank, self.ws, off, n, scale,
+                                                  self.comm_ctas, c_void_p(s.cuda_stream))
         if rc:
             raise _ops.NativeError(f"comm_allreduce failed with code {rc}")
         self.ops.launches += 2
@@ -124,20 +183,17 @@ class PeerComm:
         s = torch.cuda.current_stream()
         p = lambda t: c_void_p(t.data_ptr()) if t is not None else c_void_p(0)  # noqa: E731
         wt = weights_table if weights_table is not None else weights.table
-        rc = self.ops.lib.b200_comm_rs_adamw(grads.table, wt, self.flags.table, self.rank, self.ws,
-                                             lo, n, p(master), p(m), p(v), p(gshard), p(hp), int(push_all),
-                                             p(gnorm_out), p(extra_norm_sq), ctas, c_void_p(s.cuda_stream))
+        if self.use_nvls and push_all and weights.mc_ptr and weights_table is None:
+            rc = self.ops.lib.b200_comm_rs_adamw_nvls(grads.table, wt, c_void_p(weights.mc_ptr), self.flags.table,
+                                                      self.rank, self.ws, lo, n, p(master), p(m), p(v), p(gshard),
+                                                      p(hp), int(push_all), p(gnorm_out), p(extra_norm_sq), ctas,
+                                                      c_void_p(s.cuda_stream))
+        else:
+            rc = self.ops.lib.b200_comm_rs_adamw(grads.table, wt, self.flags.table, self.rank, self.ws,
+                                                 lo, n, p(master), p(m), p(v), p(gshard), p(hp), int(push_all),
+                                                 p(gnorm_out), p(extra_norm_sq), ctas, c_void_p(s.cuda_stream))
         if rc:
             raise _ops.NativeError(f"comm_rs_adamw failed with code {rc}")
-        self.ops.launches += 2
-
-    def push_ranges(self, weights: PeerBuffer, ranges_dev: torch.Tensor) -> None:
-        s = torch.cuda.current_stream()
-        rc = self.ops.lib.b200_comm_push_ranges(weights.table, self.flags.table, self.rank, self.ws,
-                                                c_void_p(ranges_dev.data_ptr()), ranges_dev.shape[0],
-                                                c_void_p(s.cuda_stream))
-        if rc:
-            raise _ops.NativeError(f"comm_push_ranges failed with code {rc}")
         self.ops.launches += 2
 
     def adjusted_table(self, buf: PeerBuffer, shard_elems: int, elem_size: int = 2):
@@ -168,6 +224,8 @@ class PeerComm:
         if dist.is_initialized():
             dist.barrier()
         for pb in self.buffers.values():
+            if pb.handle is not None:
+                continue
             for r, pp in enumerate(pb.peer_ptrs):
                 if r != self.rank:
                     self.ops.lib.b200_peer_close(c_void_p(pp))
@@ -175,5 +233,7 @@ class PeerComm:
             dist.barrier()
         for pb in self.buffers.values():
             pb.tensor = None
-            self.ops.lib.b200_peer_free(c_void_p(pb.local_ptr))
+            if pb.handle is None:
+                self.ops.lib.b200_peer_free(c_void_p(pb.local_ptr))
+            pb.handle = None                  # symmetric memory: dropping the tensor and the handle unmaps it
         self.buffers.clear()

@@ -12,8 +12,10 @@
 //                            global-norm clipping and AdamW on the fp32 master/moments, and stores the
 //                            updated bf16 weights into every peer's weight buffer (ZeRO-2) or only its
 //                            own shard (ZeRO-3 / FSDP)
-//   peer_push_ranges         replicates a list of small owned ranges (biases, LayerNorm vectors) to all
-//                            peers (ZeRO-3 "persistent" parameters)
+//   K13-NVLS                 the same all-reduce through an NVSwitch multicast mapping: multimem.ld_reduce sums
+//                            the ranks' copies inside the switch, multimem.st writes the result to every rank
+// Every kernel can also run as ONE cooperative launch that plays all ranks (gridDim.y = ranks, rank = blockIdx.y)
+// over per-"rank" buffers on a single GPU: that is how the protocols are tested where only one GPU exists.
 // Every NVSwitch peer is one hop away at full bandwidth, so direct one-/two-shot algorithms are used;
 // there is no ring or tree.  Cross-rank ordering uses per-CTA flag words in peer memory
 // (st.release.sys / ld.acquire.sys) with an epoch counter kept in device memory, so the kernels
@@ -140,7 +142,8 @@ __device__ __forceinline__ uint4 pack8f(const float (&f)[8]) {
 // ----------------------------------------------------------------------------------------
 template <int WS>
 __global__ void __launch_bounds__(COMM_THREADS, 2)
-allreduce_scale_kernel(PeerPtrs grads, PeerPtrs flags, int rank, size_t off, size_t n, float scale) {
+allreduce_scale_kernel(PeerPtrs grads, PeerPtrs flags, int rank_arg, size_t off, size_t n, float scale) {
+  const int rank = rank_arg < 0 ? static_cast<int>(blockIdx.y) : rank_arg;   // < 0: one launch plays every rank
   uint32_t* local = static_cast<uint32_t*>(flags.p[rank]);
   const uint32_t epoch = local[EPOCH_OFF + 0];
   rank_barrier(flags, rank, WS, 0, 2 * epoch + 1);  // every rank's bucket is final
@@ -191,6 +194,64 @@ allreduce_scale_kernel(PeerPtrs grads, PeerPtrs flags, int rank, size_t off, siz
 }
 
 // ----------------------------------------------------------------------------------------
+// K13-NVLS: the same in-place all-reduce through an NVSwitch multicast mapping of the gradient buffer.  `mc` is
+// this rank's multicast address of the buffer (every rank's physical copy is bound to one multicast object):
+// multimem.ld_reduce returns the sum of all ranks' copies, added up inside the switch, and multimem.st writes one
+// value to every rank's copy.  Each rank reduces 1/WS of the range: a GPU receives n/WS reduced elements and
+// sends n/WS, instead of pulling (WS-1)/WS * n and pushing the same amount, and one load replaces WS loads - a
+// handful of CTAs with < 64 registers per thread saturate the links and fit on SMs next to the backward GEMMs.
+// ----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc_addr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc_addr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+template <int WS>
+__global__ void __launch_bounds__(COMM_THREADS, 4)
+allreduce_scale_nvls_kernel(__nv_bfloat16* mc, PeerPtrs flags, int rank, size_t off, size_t n, float scale) {
+  uint32_t* local = static_cast<uint32_t*>(flags.p[rank]);
+  const uint32_t epoch = local[EPOCH_OFF + 0];
+  rank_barrier(flags, rank, WS, 0, 2 * epoch + 1);  // every rank's bucket is final and visible
+  const size_t nvec = n >> 3;
+  const size_t per = (nvec + WS - 1) / WS;
+  const size_t v0 = per * rank;
+  const size_t v1 = (v0 + per < nvec) ? v0 + per : nvec;
+  __nv_bfloat16* base = mc + off;
+  constexpr int U = 4;
+  const size_t tstride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i0 = v0 + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < v1;
+       i0 += tstride * U) {
+    uint4 in[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * tstride;
+      if (i < v1) in[u] = multimem_ld_reduce_bf16x8(base + i * 8);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * tstride;
+      if (i < v1) {
+        float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        acc8(a, in[u]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] *= scale;
+        multimem_st_bf16x8(base + i * 8, pack8f(a));
+      }
+    }
+  }
+  rank_barrier(flags, rank, WS, 0, 2 * epoch + 2);  // every rank's multicast stores have landed
+}
+
+// ----------------------------------------------------------------------------------------
 // K15: reduce-scatter + (clip) + AdamW + weight push, on this rank's partition [lo, lo+n).
 // hp: see adamw_kernel (hp[7] = grad scale, hp[8] = clip norm, 0 = off).
 // ----------------------------------------------------------------------------------------
@@ -206,8 +267,12 @@ struct RsAdamParams {
   size_t lo, n;
   int rank;
   int push_all;       // 1: store updated weights to every rank (ZeRO-2); 0: own copy only
-  float* gnorm_out;   // optional: [0] = global grad norm, [1] = its square
+  float* gnorm_out;   // optional, TWO floats: [0] = global grad norm, [1] = its square
   const float* extra_norm_sq;  // optional: squared norm of gradients handled outside this kernel
+  __nv_bfloat16* weights_mc;   // optional: multicast address of the weight buffer (push_all through the switch)
+};
+struct RsAdamLoop {   // one entry per emulated rank (single-launch test mode)
+  RsAdamParams r[MAX_RANKS];
 };
 
 __device__ __forceinline__ void adam8(float* master, float* m, float* v, size_t i8,
@@ -236,8 +301,7 @@ __device__ __forceinline__ void adam8(float* master, float* m, float* v, size_t 
 }
 
 template <int WS>
-__global__ void __launch_bounds__(COMM_THREADS, 2)
-rs_adamw_kernel(const RsAdamParams p) {
+__device__ __forceinline__ void rs_adamw_body(const RsAdamParams& p) {
   uint32_t* local = static_cast<uint32_t*>(p.flags.p[p.rank]);
   const uint32_t epoch = local[EPOCH_OFF + 1];
   const float lr = p.hp[0], b1 = p.hp[1], b2 = p.hp[2], eps = p.hp[3], wd = p.hp[4];
@@ -359,7 +423,9 @@ rs_adamw_kernel(const RsAdamParams p) {
         float w[8];
         adam8(p.master, p.m, p.v, i * 8, g[u], lr, b1, b2, eps, wd, ibc1, isbc2, gscale, w);
         const uint4 o = pack8f(w);
-        if (p.push_all) {
+        if (p.push_all && p.weights_mc) {
+          multimem_st_bf16x8(p.weights_mc + p.lo + i * 8, o);      // one store, the switch replicates it
+        } else if (p.push_all) {
 #pragma unroll
           for (int r = 0; r < WS; ++r) st_peer_v4(wdst[r] + i * 8, o);
         } else {
@@ -371,29 +437,16 @@ rs_adamw_kernel(const RsAdamParams p) {
   rank_barrier(p.flags, p.rank, WS, 1, 4 * epoch + 3);  // updated weights visible everywhere
 }
 
-// ----------------------------------------------------------------------------------------
-// Replicate owned small ranges to every peer.  ranges: [n_ranges][2] = (offset, length) elements.
-// ----------------------------------------------------------------------------------------
 template <int WS>
-__global__ void __launch_bounds__(256)
-peer_push_ranges_kernel(PeerPtrs weights, PeerPtrs flags, int rank, const long long* ranges,
-                        int n_ranges) {
-  uint32_t* local = static_cast<uint32_t*>(flags.p[rank]);
-  const uint32_t epoch = local[EPOCH_OFF + 2];
-  for (int k = blockIdx.x; k < n_ranges; k += gridDim.x) {
-    const size_t off = static_cast<size_t>(ranges[2 * k]);
-    const size_t nvec = static_cast<size_t>(ranges[2 * k + 1]) >> 3;
-    const uint4* srcp = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(weights.p[rank]) + off);
-    for (size_t i = threadIdx.x; i < nvec; i += blockDim.x) {
-      const uint4 v = srcp[i];
-#pragma unroll
-      for (int r = 1; r < WS; ++r) {
-        const int pr = (rank + r) % WS;
-        st_peer_v4(static_cast<__nv_bfloat16*>(weights.p[pr]) + off + i * 8, v);
-      }
-    }
-  }
-  rank_barrier(flags, rank, WS, 2, epoch + 1);
+__global__ void __launch_bounds__(COMM_THREADS, 2)
+rs_adamw_kernel(const RsAdamParams p) {
+  rs_adamw_body<WS>(p);
+}
+// Test mode: gridDim.y = WS, slice y plays rank y (cooperative launch: the slices wait for one another).
+template <int WS>
+__global__ void __launch_bounds__(COMM_THREADS, 2)
+rs_adamw_loop_kernel(const RsAdamLoop L) {
+  rs_adamw_body<WS>(L.r[blockIdx.y]);
 }
 
 // Runs stream-ordered after each collective: advances that collective's epoch and clears the
@@ -403,6 +456,17 @@ __global__ void comm_bump_epoch_kernel(uint32_t* local, int which) {
   if (which == 1) {
     local[GRIDCTR_OFF + 0] = 0;
     local[GRIDCTR_OFF + 2] = 0;  // float 0.0f
+  }
+}
+// test mode: the epochs of every emulated rank
+__global__ void comm_bump_epoch_all_kernel(PeerPtrs flags, int ws, int which) {
+  for (int r = 0; r < ws; ++r) {
+    uint32_t* local = static_cast<uint32_t*>(flags.p[r]);
+    local[EPOCH_OFF + which] += 1;
+    if (which == 1) {
+      local[GRIDCTR_OFF + 0] = 0;
+      local[GRIDCTR_OFF + 2] = 0;
+    }
   }
 }
 
@@ -487,37 +551,88 @@ extern "C" int b200_peer_close(void* ptr) { return static_cast<int>(cudaIpcClose
 extern "C" int b200_peer_free(void* ptr) { return static_cast<int>(cudaFree(ptr)); }
 extern "C" size_t b200_comm_flag_bytes() { return FLAGBUF_WORDS * sizeof(uint32_t); }
 
-#define DISPATCH_WS(ws, CALL)            \
-  switch (ws) {                          \
-    case 2: { constexpr int W = 2; CALL; } break; \
-    case 4: { constexpr int W = 4; CALL; } break; \
-    case 8: { constexpr int W = 8; CALL; } break; \
-    default: return -7;                  \
+#define DISPATCH_WS(ws, ...)                              \
+  switch (ws) {                                           \
+    case 2: { constexpr int W = 2; __VA_ARGS__; } break;  \
+    case 4: { constexpr int W = 4; __VA_ARGS__; } break;  \
+    case 8: { constexpr int W = 8; __VA_ARGS__; } break;  \
+    default: return -7;                                   \
   }
+
+// A kernel whose CTAs wait for one another (flag barriers across ranks, the grid barrier of the clipping path)
+// only finishes if all of its CTAs are resident at the same time.  Clamp the grid to what the device can hold
+// (occupancy x SM count), and launch cooperatively where CTAs of ONE grid wait for each other, so that a grid
+// that cannot be co-resident is refused with an error code instead of spinning into the trap.
+template <typename K>
+static int resident_cta_limit(K kernel, int threads) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return per_sm * device_sm_count();
+}
+static int clamp_ctas(int ctas, int dflt, int limit) {
+  if (ctas < 1) ctas = dflt;
+  if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
+  if (limit > 0 && ctas > limit) ctas = limit;
+  return ctas;
+}
 
 // ---- K13 -------------------------------------------------------------------------------------
 extern "C" int b200_comm_allreduce(void* const* grads, void* const* flags, int rank, int ws,
                                    size_t off, size_t n, float scale, int ctas, void* stream) {
   if (n % 8 || off % 8) return -2;
-  if (ctas < 1) ctas = 64;
-  if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   PeerPtrs g = make_ptrs(grads, ws), f = make_ptrs(flags, ws);
-  DISPATCH_WS(ws, (allreduce_scale_kernel<W><<<ctas, COMM_THREADS, 0, s>>>(g, f, rank, off, n, scale)));
+  DISPATCH_WS(ws, {
+    ctas = clamp_ctas(ctas, 64, resident_cta_limit(allreduce_scale_kernel<W>, COMM_THREADS));
+    allreduce_scale_kernel<W><<<ctas, COMM_THREADS, 0, s>>>(g, f, rank, off, n, scale);
+  });
   comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 0);
   return static_cast<int>(cudaGetLastError());
 }
 
-// ---- K15 -------------------------------------------------------------------------------------
-extern "C" int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* flags,
-                                  int rank, int ws, size_t lo, size_t n, float* master, float* m,
-                                  float* v, void* gshard, const float* hp, int push_all,
-                                  float* gnorm_out, const float* extra_norm_sq, int ctas,
-                                  void* stream) {
-  if (n % 8 || lo % 8) return -2;
-  if (ctas < 1) ctas = 64;
-  if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
+// K13 through the NVSwitch multicast mapping of the gradient buffer (mc_base = this rank's multicast address).
+extern "C" int b200_comm_allreduce_nvls(void* mc_base, void* const* flags, int rank, int ws, size_t off,
+                                        size_t n, float scale, int ctas, void* stream) {
+  if ((off % 8) || (n % 8) || ws > MAX_RANKS || !mc_base) return -2;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  PeerPtrs f = make_ptrs(flags, ws);
+  __nv_bfloat16* mc = static_cast<__nv_bfloat16*>(mc_base);
+  DISPATCH_WS(ws, {
+    ctas = clamp_ctas(ctas, 16, resident_cta_limit(allreduce_scale_nvls_kernel<W>, COMM_THREADS));
+    allreduce_scale_nvls_kernel<W><<<ctas, COMM_THREADS, 0, s>>>(mc, f, rank, off, n, scale);
+  });
+  comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 0);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// Test mode of K13: ONE cooperative launch plays all ws ranks (gridDim.y = ws) over per-rank buffers that all
+// live on the current GPU.  grads[r] / flags[r] are rank r's buffers.
+extern "C" int b200_comm_allreduce_loop(void* const* grads, void* const* flags, int ws, size_t off, size_t n,
+                                        float scale, int ctas, void* stream) {
+  if (n % 8 || off % 8) return -2;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  PeerPtrs g = make_ptrs(grads, ws), f = make_ptrs(flags, ws);
+  int rank = -1;
+  void* args[] = {&g, &f, &rank, &off, &n, &scale};
+  DISPATCH_WS(ws, {
+    ctas = clamp_ctas(ctas, 8, resident_cta_limit(allreduce_scale_kernel<W>, COMM_THREADS) / ws);
+    if (ctas < 1) return -9;
+    cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(allreduce_scale_kernel<W>), dim3(ctas, ws),
+                                                dim3(COMM_THREADS), args, 0, s);
+    if (e != cudaSuccess) return static_cast<int>(e);
+  });
+  comm_bump_epoch_all_kernel<<<1, 1, 0, s>>>(f, ws, 0);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- K15 -------------------------------------------------------------------------------------
+static RsAdamParams make_rs_params(void* const* grads, void* const* weights, void* const* flags, int rank, int ws,
+                                   size_t lo, size_t n, float* master, float* m, float* v, void* gshard,
+                                   const float* hp, int push_all, float* gnorm_out, const float* extra_norm_sq,
+                                   void* weights_mc) {
   RsAdamParams p;
   p.grads = make_ptrs(grads, ws);
   p.weights = make_ptrs(weights, ws);
@@ -533,19 +648,81 @@ extern "C" int b200_comm_rs_adamw(void* const* grads, void* const* weights, void
   p.push_all = push_all;
   p.gnorm_out = gnorm_out;
   p.extra_norm_sq = extra_norm_sq;
-  DISPATCH_WS(ws, (rs_adamw_kernel<W><<<ctas, COMM_THREADS, 0, s>>>(p)));
+  p.weights_mc = static_cast<__nv_bfloat16*>(weights_mc);
+  return p;
+}
+
+static int rs_adamw_launch(const RsAdamParams& p, int ws, int ctas, cudaStream_t s) {
+  RsAdamParams pp = p;
+  void* args[] = {&pp};
+  DISPATCH_WS(ws, {
+    const int limit = resident_cta_limit(rs_adamw_kernel<W>, COMM_THREADS);
+    ctas = clamp_ctas(ctas, 64, limit);
+    if (ctas < 1) return -9;
+    // cooperative: the clipping path has a grid barrier; a grid that cannot be resident is refused, not trapped
+    cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(rs_adamw_kernel<W>), dim3(ctas),
+                                                dim3(COMM_THREADS), args, 0, s);
+    if (e != cudaSuccess) return static_cast<int>(e);
+  });
+  return 0;
+}
+
+extern "C" int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* flags,
+                                  int rank, int ws, size_t lo, size_t n, float* master, float* m,
+                                  float* v, void* gshard, const float* hp, int push_all,
+                                  float* gnorm_out, const float* extra_norm_sq, int ctas,
+                                  void* stream) {
+  if (n % 8 || lo % 8) return -2;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const RsAdamParams p = make_rs_params(grads, weights, flags, rank, ws, lo, n, master, m, v, gshard, hp, push_all,
+                                        gnorm_out, extra_norm_sq, nullptr);
+  const int rc = rs_adamw_launch(p, ws, ctas, s);
+  if (rc) return rc;
   comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 1);
   return static_cast<int>(cudaGetLastError());
 }
 
-extern "C" int b200_comm_push_ranges(void* const* weights, void* const* flags, int rank, int ws,
-                                     const long long* ranges_dev, int n_ranges, void* stream) {
+// K15 whose weight push (push_all = 1) goes through the multicast mapping of the weight buffer: one
+// multimem.st per 16 bytes instead of ws peer stores.
+extern "C" int b200_comm_rs_adamw_nvls(void* const* grads, void* const* weights, void* weights_mc,
+                                       void* const* flags, int rank, int ws, size_t lo, size_t n, float* master,
+                                       float* m, float* v, void* gshard, const float* hp, int push_all,
+                                       float* gnorm_out, const float* extra_norm_sq, int ctas, void* stream) {
+  if (n % 8 || lo % 8) return -2;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  PeerPtrs w = make_ptrs(weights, ws), f = make_ptrs(flags, ws);
-  int ctas = n_ranges < COMM_MAX_CTAS ? n_ranges : COMM_MAX_CTAS;
-  if (ctas < 1) ctas = 1;
-  DISPATCH_WS(ws, (peer_push_ranges_kernel<W><<<ctas, 256, 0, s>>>(w, f, rank, ranges_dev, n_ranges)));
-  comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 2);
+  const RsAdamParams p = make_rs_params(grads, weights, flags, rank, ws, lo, n, master, m, v, gshard, hp, push_all,
+                                        gnorm_out, extra_norm_sq, weights_mc);
+  const int rc = rs_adamw_launch(p, ws, ctas, s);
+  if (rc) return rc;
+  comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 1);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// Test mode of K15: one cooperative launch plays all ranks.  Per-rank arrays (length ws): lo, master, m, v,
+// gshard, hp, gnorm_out (nullable entries), extra_norm_sq (nullable entries); n is the common partition size.
+extern "C" int b200_comm_rs_adamw_loop(void* const* grads, void* const* weights, void* const* flags, int ws,
+                                       const size_t* lo, size_t n, float* const* master, float* const* m,
+                                       float* const* v, void* const* gshard, const float* const* hp, int push_all,
+                                       float* const* gnorm_out, const float* const* extra_norm_sq, int ctas,
+                                       void* stream) {
+  if (n % 8 || ws > MAX_RANKS) return -2;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  RsAdamLoop L;
+  memset(&L, 0, sizeof(L));
+  for (int r = 0; r < ws; ++r) {
+    if (lo[r] % 8) return -2;
+    L.r[r] = make_rs_params(grads, weights, flags, r, ws, lo[r], n, master[r], m[r], v[r], gshard[r], hp[r], push_all,
+                            gnorm_out ? gnorm_out[r] : nullptr, extra_norm_sq ? extra_norm_sq[r] : nullptr, nullptr);
+  }
+  void* args[] = {&L};
+  DISPATCH_WS(ws, {
+    ctas = clamp_ctas(ctas, 8, resident_cta_limit(rs_adamw_loop_kernel<W>, COMM_THREADS) / ws);
+    if (ctas < 1) return -9;
+    cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(rs_adamw_loop_kernel<W>), dim3(ctas, ws),
+                                                dim3(COMM_THREADS), args, 0, s);
+    if (e != cudaSuccess) return static_cast<int>(e);
+  });
+  comm_bump_epoch_all_kernel<<<1, 1, 0, s>>>(L.r[0].flags, ws, 1);
   return static_cast<int>(cudaGetLastError());
 }
 

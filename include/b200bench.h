@@ -155,12 +155,35 @@ int b200_comm_allreduce(void* const* grads, void* const* flags, int rank, int ws
 /* K15: this rank's partition [lo, lo+n): g = sum over ranks of grads; optional global-norm clip
  * (hp[8]); AdamW on fp32 master/m/v; bf16 weights stored to every rank (push_all=1, ZeRO-2) or to
  * the own buffer only (ZeRO-3 / FSDP).  gshard: n bf16 of local scratch. hp as in b200_adamw.
- * gnorm_out (nullable, 2 floats): norm and squared norm; extra_norm_sq (nullable): squared norm of
+ * gnorm_out (nullable, TWO floats): norm and squared norm; extra_norm_sq (nullable): squared norm of
  * gradients that are updated outside this kernel (the replicated small tensors under ZeRO-3). */
+/* Every CTA count is clamped to what the device can hold at once (occupancy x SMs); K15 is launched cooperatively
+ * because its clipping path has a barrier over the whole grid: a grid that cannot be co-resident is refused with a
+ * CUDA error instead of spinning. */
 int b200_comm_rs_adamw(void* const* grads, void* const* weights, void* const* flags, int rank,
                        int ws, size_t lo, size_t n, float* master, float* m, float* v, void* gshard,
                        const float* hp, int push_all, float* gnorm_out, const float* extra_norm_sq,
                        int ctas, void* stream);
+/* K13 / K15 through an NVSwitch multicast (NVLS) mapping.  mc_base / weights_mc = THIS rank's multicast address of
+ * the buffer (every rank's physical copy bound to one multicast object, e.g. by torch's symmetric memory):
+ * multimem.ld_reduce sums the ranks' copies inside the switch, multimem.st writes all copies with one store. */
+int b200_comm_allreduce_nvls(void* mc_base, void* const* flags, int rank, int ws, size_t off, size_t n,
+                             float scale, int ctas, void* stream);
+int b200_comm_rs_adamw_nvls(void* const* grads, void* const* weights, void* weights_mc, void* const* flags,
+                            int rank, int ws, size_t lo, size_t n, float* master, float* m, float* v, void* gshard,
+                            const float* hp, int push_all, float* gnorm_out, const float* extra_norm_sq, int ctas,
+                            void* stream);
+/* Single-GPU test mode of K13 / K15: ONE cooperative launch plays all ws ranks (gridDim.y = ws, rank = blockIdx.y)
+ * over per-rank buffers that all live on the current device; grads[r] / weights[r] / flags[r] and the per-rank
+ * arrays (length ws) belong to emulated rank r.  Separate launches per rank on one GPU are NOT an option: kernels
+ * that wait for one another are not guaranteed to run at the same time.  Returns -9 if the device cannot hold
+ * the whole grid at once. */
+int b200_comm_allreduce_loop(void* const* grads, void* const* flags, int ws, size_t off, size_t n, float scale,
+                             int ctas, void* stream);
+int b200_comm_rs_adamw_loop(void* const* grads, void* const* weights, void* const* flags, int ws, const size_t* lo,
+                            size_t n, float* const* master, float* const* m, float* const* v, void* const* gshard,
+                            const float* const* hp, int push_all, float* const* gnorm_out,
+                            const float* const* extra_norm_sq, int ctas, void* stream);
 /* GEMM launches use programmatic dependent launch (their prologue overlaps the previous kernel's tail;
  * the kernel waits with griddepcontrol.wait before touching global memory).  0 turns it off. */
 int b200_set_gemm_pdl(int on);
@@ -199,9 +222,6 @@ int b200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
 int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst, unsigned long long flat_off,
                            unsigned long long n, unsigned long long shard_elems, int ctas,
                            void* stream);
-/* Copies owned small ranges (device array of (offset, length) pairs, elements) to every peer. */
-int b200_comm_push_ranges(void* const* weights, void* const* flags, int rank, int ws,
-                          const long long* ranges_dev, int n_ranges, void* stream);
 /* dst[i] = src[i] with 16-byte volatile loads: P2P bandwidth probe when src is peer memory. */
 int b200_peer_copy(const void* src, void* dst, size_t bytes, int ctas, void* stream);
 

@@ -59,6 +59,9 @@ def main():
     # ---- K13 all-reduce ------------------------------------------------------------------------
     n = 8 * 1024 * 1024 + 128 * 3
     gb = comm.alloc("g", n, torch.bfloat16)
+    if rank == 0:
+        print(f"[check] allocation: {'symmetric memory' if gb.handle is not None else 'cudaMalloc + CUDA IPC'}, "
+              f"multicast address {'yes (NVLS kernels)' if gb.mc_ptr else 'no (peer load/store kernels)'}", flush=True)
     torch.manual_seed(100 + rank)
     src = (torch.randn(n, device=dev) * 0.5).to(torch.bfloat16)
     gb.tensor.copy_(src)
@@ -92,7 +95,7 @@ def main():
         gsh = torch.zeros(shard, dtype=torch.bfloat16, device=dev)
         hp = torch.zeros(16, device=dev)
         ops.adamw_set_hp(hp, 1e-2, 0.9, 0.999, 1e-8, 0.01, 1 / (1 - 0.9), 1 / math.sqrt(1 - 0.999), 1.0 / ws, clip)
-        gn = torch.zeros(1, device=dev)
+        gn = torch.zeros(2, device=dev)      # K15 writes the norm and its square
         comm.rs_adamw(gb, wb, lo, shard, master, m, v, gsh, hp, push_all=True, gnorm_out=gn)
         torch.cuda.synchronize(dev)
         # reference: NCCL all-reduce, then the single-GPU AdamW kernel on the shard
@@ -113,7 +116,7 @@ def main():
         e_push = (wb.tensor[:shard * ws].float() - full.float()).abs().max().item()
         extra = f"master_err={e_master:.2e} push_err={e_push:.2e}"
         if clip > 0:
-            extra += f" norm={gn.item():.3f} ref={math.sqrt(ss.item()):.3f}"
+            extra += f" norm={gn[0].item():.3f} ref={math.sqrt(ss.item()):.3f}"
         report(f"K15 rs_adamw clip={clip}", e_master < 2e-3 and e_push < 2e-2, extra)
 
     # ---- engine: fused vs NCCL schedule, same data, dropout 0 ----------------------------------------
