@@ -86,8 +86,15 @@ __device__ __forceinline__ void rank_barrier(const PeerPtrs& flags, int rank, in
     const uint32_t* src = static_cast<const uint32_t*>(flags.p[rank]) +
                           (kind * COMM_MAX_CTAS + blockIdx.x) * MAX_RANKS + peer;
     uint32_t spins = 0;
+    uint64_t t0 = 0;
     while (static_cast<int32_t>(ld_acquire_sys(src) - value) < 0) {
-      if (++spins > (1u << 28)) {  // a peer never arrived: abort instead of hanging
+      bool expired = false;
+      if ((++spins & 255u) == 0) {       // wall-clock bound (20 s: ranks may reach a collective seconds apart)
+        const uint64_t now = global_timer_ns();
+        if (t0 == 0) t0 = now;
+        expired = now - t0 > 5 * kWaitTimeoutNs;
+      }
+      if (expired) {  // a peer never arrived: abort instead of hanging
 #ifdef B200_COMM_DEBUG
         printf("[b200 comm] rank %d CTA %d: rank %d never reached flag plane %d value %u (last seen %u)\n", rank,
                static_cast<int>(blockIdx.x), peer, kind, value, ld_acquire_sys(src));
@@ -106,8 +113,15 @@ __device__ __forceinline__ void grid_barrier(uint32_t* ctr, uint32_t target) {
     __threadfence();
     atomicAdd(ctr, 1u);
     uint32_t spins = 0;
+    uint64_t t0 = 0;
     while (static_cast<int32_t>(ld_acquire_gpu(ctr) - target) < 0) {
-      if (++spins > (1u << 28)) {
+      bool expired = false;
+      if ((++spins & 255u) == 0) {
+        const uint64_t now = global_timer_ns();
+        if (t0 == 0) t0 = now;
+        expired = now - t0 > 5 * kWaitTimeoutNs;
+      }
+      if (expired) {
 #ifdef B200_COMM_DEBUG
         printf("[b200 comm] CTA %d: grid barrier stuck at %u of %u\n", static_cast<int>(blockIdx.x),
                ld_acquire_gpu(ctr), target);
@@ -226,7 +240,7 @@ allreduce_scale_nvls_kernel(__nv_bfloat16* mc, PeerPtrs flags, int rank, size_t 
   const size_t v0 = per * rank;
   const size_t v1 = (v0 + per < nvec) ? v0 + per : nvec;
   __nv_bfloat16* base = mc + off;
-  constexpr int U = 4;
+  constexpr int U = 8;      // a switch reduction takes a few microseconds: depth, not occupancy, hides it
   const size_t tstride = static_cast<size_t>(gridDim.x) * blockDim.x;
   for (size_t i0 = v0 + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < v1;
        i0 += tstride * U) {

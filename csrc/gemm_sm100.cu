@@ -21,10 +21,12 @@
 // K14 (the FSDP / ZeRO-3 parameter all-gather, TH:229-237,366) lives in the producer warp:
 // when B is a weight matrix that is partitioned over ranks, there is one tensor map per OWNING rank over
 // that rank's shard as mapped into this process (peer memory over NVLink), and every B tile is fetched by
-// TMA straight from its owner into shared memory - no gather pass, no staging copy in HBM, no flags.  Peer
-// data is not cached by the local L2, so the CTAs (or CTA pairs) that work on the same N-tile for different
-// M-tiles form ONE thread-block cluster: each of them fetches 1/P of the B tile and multicasts it to the
-// others (.multicast::cluster), so a remote tile crosses NVLink once per cluster, not once per CTA.
+// TMA straight from its owner into shared memory - no gather pass, no staging copy in HBM, no flags.
+// The kernel can also share B inside a thread-block cluster: the CTAs (or CTA pairs) that work on the same N-tile
+// for different M-tiles each fetch 1/P of the B tile and multicast it to the others (.multicast::cluster).  That
+// is meant for exactly the remote case (peer data is not cached by the local L2, so every CTA that needs a tile
+// pulls it over NVLink again), but multicast loads FROM peer memory are switched off - see gemm_impl - so today it
+// only serves a local B.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -815,11 +817,17 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   const int b_rows = b_mn ? K : N;      // rows of the stored weight matrix
   // bn_hint: 0 = auto, 128 / 256 = single-CTA tile width, 2128 / 2256 = CTA-pair (cta_group::2) mode
   int BN = bn_hint % 1000, CTAS = bn_hint >= 2000 ? 2 : 1;
-  int want_units = ex ? ex->mc_units : 0;   // 0 = auto: multicast only when B comes from peers
+  // Cluster multicast of B is only used for a LOCAL B.  On this driver (580.159, B200) a TMA multicast load whose
+  // source is peer memory (cp.async.bulk.tensor ... .multicast::cluster from an NVLink-mapped address) stopped the
+  // GPU outright in two separate 2-GPU runs - no trap, no Xid the process could see, the device just went away -
+  // while the same kernel is correct with unicast TMA from peers (tests/multi/check_k14.py) and with multicast
+  // from local memory (tests/test_kernels_gpu.py).  So a partitioned B is always fetched unicast, per CTA.
+  if (b_ws > 1 && ex && ex->mc_units > 1) return -2;
+  int want_units = (b_ws > 1) ? 1 : (ex ? ex->mc_units : 0);   // 0 = auto = off
   // Units per cluster for a (bn, ctas) candidate: as many consecutive M-tiles as there are (<= 8, power of two),
   // every TMA box of B a multiple of 8 rows, and no box may straddle two owners.
   auto units_for = [&](int bn, int ctas) {
-    int want = want_units > 0 ? want_units : (b_ws > 1 ? GEMM_MAX_UNITS : 1);
+    int want = want_units > 0 ? want_units : 1;
     int u = 1;
     while (u * 2 <= want && u * 2 <= GEMM_MAX_UNITS && u * 2 * 128 * ctas <= ((M + 127) / 128) * 128) u *= 2;
     for (; u >= 1; u >>= 1) {

@@ -81,13 +81,24 @@ __device__ __forceinline__ bool mbar_test(uint32_t bar_addr, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug traps (kernel aborts with an error) instead of hanging the GPU.
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr uint64_t kWaitTimeoutNs = 4000000000ull;    // 4 s: far beyond any legitimate wait inside one kernel
+// Bounded wait: a protocol bug traps (kernel aborts with an error) instead of hanging the GPU.  The bound is
+// wall-clock time (try_wait sleeps in hardware for an unspecified while, so counting iterations bounds nothing).
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
+  if (mbar_test(addr, parity)) return;
   uint32_t spins = 0;
+  uint64_t t0 = 0;
   while (!mbar_test(addr, parity)) {
-    if (++spins > (1u << 26)) {  // try_wait sleeps in HW; this is many seconds
-      __trap();
+    if ((++spins & 1023u) == 0) {
+      const uint64_t now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kWaitTimeoutNs) __trap();
     }
   }
 }

@@ -312,10 +312,10 @@ int main(int argc, char** argv) {
       {2048, 512, 256, 0, 0, B200_EPI_BIAS_GELU, 2256, 8},
       {2048, 1024, 512, 0, 1, B200_EPI_DGELU, 2256, 8},
       {1000, 520, 200, 0, 0, B200_EPI_BIAS_RESID, 2256, 4},
-      // ---- K14: B fetched per owner from separate allocations (emulated ranks), with and without multicast ----
+      // ---- K14: B fetched per owner from separate allocations (emulated ranks) ----
       {256, 384, 256, 0, 0, B200_EPI_BIAS, 2128, 1, 2},
       {256, 384, 256, 0, 1, B200_EPI_NONE, 128, 1, 4},
-      {512, 512, 512, 0, 0, B200_EPI_BIAS, 2256, 2, 4},
+      {512, 512, 512, 0, 0, B200_EPI_BIAS, 2256, 1, 4},
       {2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 0, 0, 8},
       {2048, 1024, 3072, 0, 1, B200_EPI_NONE, 0, 0, 8},
       {2048, 1024, 4096, 0, 0, B200_EPI_BIAS_RESID, 0, 0, 4},

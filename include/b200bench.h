@@ -200,8 +200,9 @@ int b200_set_gemm_pdl(int on);
  *                        Replaces FSDP's pre-forward all-gather / ZeRO-3's per-module gathers (TH:229-237,366;
  *                        SURVEY N4,N8).  Returns -9 when no tile shape keeps every TMA box inside one owner.
  *  mc_units              tile units (CTAs / CTA pairs along M) per thread-block cluster that share each B tile by
- *                        TMA multicast: 0 = auto (off for local B, as many as cover M, <= 8, for partitioned B),
- *                        1 = off, 2 / 4 / 8 = forced. */
+ *                        TMA multicast: 0 / 1 = off, 2 / 4 / 8 = that many.  Local B only: with a partitioned B
+ *                        (b_ws > 1) any value > 1 is rejected (-2) - multicast TMA loads from peer memory took
+ *                        the GPU down on driver 580.159, see csrc/gemm_sm100.cu. */
 typedef struct B200GemmEx {
   void* dbias;
   int dbias_accum;

@@ -164,15 +164,21 @@ def main():
                 print(f"[bench] P2P read {nbytes/2**20:.0f} MiB, {ctas} CTAs: {ms*1e3:.0f} us  {nbytes/ms/1e6:.0f} GB/s", flush=True)
         for mb in (1, 8, 25, 64, 256):
             cnt = mb * 1024 * 1024 // 2
-            for ctas in (32, 64, 128):
-                comm.comm_ctas = ctas
-                ms = timed(lambda: comm.allreduce(big, 0, cnt, 1.0 / ws, side_stream=False), 10, ws, dev)
-                bus = 2 * (ws - 1) / ws * cnt * 2 / ms / 1e6
-                t = big.tensor[:cnt]
-                ms_n = timed(lambda: dist.all_reduce(t), 10, ws, dev)
+            t = big.tensor[:cnt]
+            ms_n = timed(lambda: dist.all_reduce(t), 10, ws, dev)
+            for ctas in (8, 16, 32, 64, 128):
+                comm.comm_ctas = comm.nvls_ctas = ctas
+                res = {}
+                for mode in ("nvls", "p2p"):
+                    if mode == "nvls" and not big.mc_ptr:
+                        continue
+                    comm.use_nvls = mode == "nvls"
+                    res[mode] = timed(lambda: comm.allreduce(big, 0, cnt, 1.0 / ws, side_stream=False), 10, ws, dev)
+                comm.use_nvls = True
                 if rank == 0:
-                    print(f"[bench] allreduce {mb:4d} MiB ctas={ctas:3d}: fused {ms*1e3:8.1f} us (busbw {bus:6.0f} GB/s)   "
-                          f"nccl {ms_n*1e3:8.1f} us", flush=True)
+                    txt = "  ".join(f"{k} {v*1e3:8.1f} us (busbw {2 * (ws - 1) / ws * cnt * 2 / v / 1e6:5.0f} GB/s)"
+                                    for k, v in res.items())
+                    print(f"[bench] allreduce {mb:4d} MiB ctas={ctas:3d}: {txt}   nccl {ms_n*1e3:8.1f} us", flush=True)
         # K15 on a tier-A-sized buffer (236.4 M elements): reduce-scatter + AdamW (+ push to every peer)
         nk = 236_400_000 // (8 * ws) * (8 * ws)
         gk = comm.alloc("gk", nk, torch.bfloat16)
