@@ -79,6 +79,7 @@ class StrategyConfig:
     # gradient accumulation: "reference" = only ZeRO strategies honour --grad-accum
     grad_accum_mode: str = "reference"
     raw: Dict[str, Any] = field(default_factory=dict)
+    notes: list = field(default_factory=list)     # how non-native values of a strategy file were interpreted
 
     def to_dict(self) -> Dict[str, Any]:
         return asdict(self)
@@ -102,6 +103,60 @@ def _apply_engine_knobs(cfg: "StrategyConfig", section: Dict[str, Any]) -> None:
             setattr(cfg, key, v)
 
 
+# ---- strict key handling: every key of a strategy file is either applied, or accepted only with the one value
+# that matches what the engine does anyway, or rejected.  Nothing is parsed and then silently ignored.
+_DS_TOP_HONOURED = {"zero_optimization", "bf16", "optimizer", "scheduler", "gradient_clipping", "b200bench",
+                    "train_batch_size", "train_micro_batch_size_per_gpu", "gradient_accumulation_steps", "_doc"}
+# reporting-only keys of DeepSpeed: no effect on the computation, any value accepted
+_DS_TOP_INERT = {"steps_per_print", "wall_clock_breakdown", "flops_profiler", "zero_allow_untested_optimizer"}
+_DS_ZERO_HONOURED = {"stage", "overlap_comm", "reduce_bucket_size", "stage3_prefetch_bucket_size",
+                     "stage3_param_persistence_threshold", "stage3_max_live_parameters", "offload_optimizer",
+                     "offload_param"}
+# keys whose only supported value is the one the flat-buffer engine implements by construction
+_DS_ZERO_FIXED = {
+    "contiguous_gradients": (True, "gradients always live in one flat buffer"),
+    "reduce_scatter": (True, "gradients are always reduce-scattered into the owning partition (K15)"),
+    "allgather_partitions": (True, "updated partitions are always pushed to every rank by K15"),
+    "round_robin_gradients": (None, "partitions are contiguous ranges of the flat buffer; accepted, no effect"),
+    "stage3_gather_16bit_weights_on_model_save": (True, "state_dict() always gathers the bf16 weights"),
+}
+# size hints that are upper bounds in DeepSpeed and are satisfied by construction here (one fused launch)
+_DS_ZERO_BOUNDS = {"allgather_bucket_size", "sub_group_size", "stage3_max_reuse_distance"}
+
+
+def _check_deepspeed_keys(raw: Dict[str, Any]) -> None:
+    for k in raw:
+        if k not in _DS_TOP_HONOURED and k not in _DS_TOP_INERT:
+            raise ValueError(f"DeepSpeed config key {k!r} is not supported by b200bench (it would be ignored)")
+    if raw.get("bf16", {}).get("enabled", True) is not True:
+        raise ValueError("bf16.enabled must be true: the native engine computes in bf16 with fp32 master weights")
+    if raw.get("fp16", {}).get("enabled", False):
+        raise ValueError("fp16 is not supported (bf16 needs no loss scaling)")
+    opt_type = raw.get("optimizer", {}).get("type", "AdamW")
+    if opt_type not in ("AdamW", "Adam"):
+        raise ValueError(f"optimizer.type {opt_type!r} is not supported (AdamW)")
+    sched = raw.get("scheduler", {}).get("type")
+    if sched not in (None, "WarmupLR"):
+        raise ValueError(f"scheduler.type {sched!r} is not supported (WarmupLR or none)")
+    z = raw.get("zero_optimization", {})
+    if int(z.get("stage", 0)) not in (2, 3):
+        raise ValueError(f"zero_optimization.stage must be 2 or 3, got {z.get('stage')!r}")
+    for k, v in z.items():
+        if k in _DS_ZERO_HONOURED or k in _DS_ZERO_BOUNDS:
+            continue
+        if k in _DS_ZERO_FIXED:
+            want, why = _DS_ZERO_FIXED[k]
+            if want is not None and v is not want:
+                raise ValueError(f"zero_optimization.{k}={v!r} is not supported: {why}")
+            continue
+        raise ValueError(f"zero_optimization.{k} is not supported by b200bench (it would be ignored)")
+
+
+_FSDP_KEYS = {"sharding_strategy", "auto_wrap_policy", "backward_prefetch", "forward_prefetch", "sync_module_states",
+              "reshard_after_forward", "param_gather", "gather_ctas", "comm_ctas", "mixed_precision", "cpu_offload",
+              "ddp_bucket_cap_mb"}
+
+
 def load_deepspeed_config(path: str, micro_batch: int, grad_accum: int, world_size: int) -> StrategyConfig:
     """Parse a DeepSpeed-format JSON.  The three batch keys are replaced by integers computed
     from the CLI, as the reference does at ``TH:251-262``."""
@@ -112,6 +167,7 @@ def load_deepspeed_config(path: str, micro_batch: int, grad_accum: int, world_si
     raw["train_micro_batch_size_per_gpu"] = int(micro_batch)
     raw["gradient_accumulation_steps"] = int(grad_accum)
     raw["train_batch_size"] = int(micro_batch) * int(grad_accum) * int(world_size)
+    _check_deepspeed_keys(raw)
 
     cfg = StrategyConfig(raw=raw)
     cfg.optim.grad_clip = float(raw.get("gradient_clipping", 0.0))
@@ -153,9 +209,37 @@ def load_fsdp_config(path: Optional[str]) -> StrategyConfig:
         raw = yaml.safe_load(f) or {}
     body = raw.get("fsdp_config", raw)
     cfg.raw = raw
-    cfg.fsdp_sharding_strategy = str(body.get("sharding_strategy", cfg.fsdp_sharding_strategy))
-    cfg.fsdp_auto_wrap_policy = str(body.get("auto_wrap_policy", cfg.fsdp_auto_wrap_policy))
-    cfg.fsdp_backward_prefetch = str(body.get("backward_prefetch", cfg.fsdp_backward_prefetch))
+    for k in body:
+        if k not in _FSDP_KEYS:
+            raise ValueError(f"FSDP config key {k!r} is not supported by b200bench (it would be ignored)")
+    cfg.fsdp_sharding_strategy = str(body.get("sharding_strategy", cfg.fsdp_sharding_strategy)).lower()
+    if cfg.fsdp_sharding_strategy not in ("full_shard", "shard_grad_op", "no_shard"):
+        raise ValueError(f"sharding_strategy must be full_shard, shard_grad_op or no_shard, got "
+                         f"{cfg.fsdp_sharding_strategy!r} (hybrid sharding needs more than one node)")
+    awp = str(body.get("auto_wrap_policy", cfg.fsdp_auto_wrap_policy)).lower()
+    if awp == "size_based":
+        # the reference's stock file (configs/fsdp/fsdp_config.yaml:6 there): its policy wraps nothing at these
+        # model sizes, i.e. ONE flat unit without overlap.  Accepted so that the file loads; the
+        # engine's gather unit is the transformer block, and that is said out loud.
+        cfg.notes.append("auto_wrap_policy: size_based read as transformer_block (the engine's gather unit is one "
+                         "transformer block; the reference's size-based policy yields a single flat unit)")
+        awp = "transformer_block"
+    if awp != "transformer_block":
+        raise ValueError(f"auto_wrap_policy must be transformer_block (or the reference's size_based), got {awp!r}")
+    cfg.fsdp_auto_wrap_policy = awp
+    cfg.fsdp_backward_prefetch = str(body.get("backward_prefetch", cfg.fsdp_backward_prefetch)).lower()
+    if cfg.fsdp_backward_prefetch not in ("backward_pre", "backward_post", "none"):
+        raise ValueError(f"backward_prefetch must be backward_pre, backward_post or none, got "
+                         f"{cfg.fsdp_backward_prefetch!r}")
+    mp = body.get("mixed_precision", "bf16")
+    if mp is False or str(mp).lower() in ("false", "none"):
+        # reference file: "false # handled by autocast" - there fp16 autocast over fp32 weights (TH:334-376)
+        cfg.notes.append("mixed_precision: false read as bf16 (the reference leaves precision to fp16 autocast; the "
+                         "native engine always computes in bf16 with fp32 master weights and optimizer state)")
+    elif str(mp).lower() != "bf16":
+        raise ValueError(f"mixed_precision must be bf16 (or the reference's false), got {mp!r}")
+    if body.get("ddp_bucket_cap_mb") is not None:
+        cfg.ddp_bucket_cap_mb = int(body["ddp_bucket_cap_mb"])
     cfg.fsdp_forward_prefetch = bool(body.get("forward_prefetch", cfg.fsdp_forward_prefetch))
     cfg.fsdp_sync_module_states = bool(body.get("sync_module_states", cfg.fsdp_sync_module_states))
     r = body.get("reshard_after_forward", cfg.fsdp_reshard_after_forward)

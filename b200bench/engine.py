@@ -37,7 +37,7 @@ from .config import StrategyConfig
 from .models.layout import ParamLayout, build_layout
 from .optim.adamw import warmup_lr
 from .parallel.collectives import DistCtx
-from .parallel.torch_engine import SHARDED_OPT, SHARDED_PARAMS, effective_grad_accum
+from .parallel.torch_engine import SHARDED_OPT, SHARDED_PARAMS, comm_strategy, effective_grad_accum
 
 BF16 = torch.bfloat16
 
@@ -70,6 +70,7 @@ class NativeEngine:
         self._regather_tables = True
         self._invalidate_staging()
         self.strategy, self.cfg, self.ctx, self.device = strategy, cfg, ctx, device
+        self.comm_strategy = cs = comm_strategy(strategy, cfg)     # fsdp follows the YAML's sharding_strategy
         self.accum = effective_grad_accum(strategy, grad_accum, cfg.grad_accum_mode)
         self.dropout, self.causal = float(dropout), bool(causal)
         self.B, self.T = int(batch), int(seq_len)
@@ -99,7 +100,7 @@ class NativeEngine:
             ctas = (int(os.environ.get("B200BENCH_COMM_CTAS", "0")) or int(getattr(cfg, "comm_ctas", 0) or 0)
                     or {2: 64, 4: 32}.get(ws, 16))
             self.comm = PeerComm(ctx, device, comm_ctas=ctas)
-        self.sharded_params = self.comm is not None and strategy in SHARDED_PARAMS
+        self.sharded_params = self.comm is not None and cs in SHARDED_PARAMS
 
         # ---- parameters / gradients ---------------------------------------------------------------
         if self.comm is not None:
@@ -113,8 +114,10 @@ class NativeEngine:
         else:
             full = torch.zeros(Lt.total, dtype=BF16, device=dev)           # temporary when sharded
         self._init_params(full, seed)
-        if ws > 1:
-            ctx.broadcast(full, 0)                                          # N2 / N9
+        # N2 / N9: rank 0's initial weights to everyone.  fsdp_config.yaml `sync_module_states: false` skips it (every
+        # rank initialises from the same seed here, so the replicas agree either way)
+        if ws > 1 and not (strategy == "fsdp" and not cfg.fsdp_sync_module_states):
+            ctx.broadcast(full, 0)
         self.hp = torch.zeros(16, dtype=torch.float32, device=dev)
         self.hp_small = torch.zeros(16, dtype=torch.float32, device=dev)
         self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -128,13 +131,13 @@ class NativeEngine:
             del full
         else:
             self.params = full
-            self.lo, self.hi = Lt.shard_range(rank) if strategy in SHARDED_OPT else (0, Lt.total)
+            self.lo, self.hi = Lt.shard_range(rank) if cs in SHARDED_OPT else (0, Lt.total)
             self.master = self.params[self.lo:self.hi].float()
             self.P = {s.name: self.params[s.offset:s.offset + s.numel].view(s.shape) for s in Lt}
         n_opt = self.hi - self.lo
         self.exp_avg = torch.zeros(n_opt, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n_opt, dtype=torch.float32, device=dev)
-        self.grad_shard = torch.zeros(n_opt, dtype=BF16, device=dev) if strategy in SHARDED_OPT else None
+        self.grad_shard = torch.zeros(n_opt, dtype=BF16, device=dev) if cs in SHARDED_OPT else None
 
         # ---- activations (allocated once) -----------------------------------------------------
         M, d, V, L = self.M, self.d, self.V, self.L
@@ -181,7 +184,7 @@ class NativeEngine:
         self.overlap_wgrad = True
         # ddp without clipping: AdamW of a block runs as soon as its gradients are final (memory-bound, it
         # hides behind the compute-bound backward of the earlier blocks); the boundary has nothing left to do
-        self.opt_in_backward = (strategy == "ddp" and not (cfg.optim.grad_clip > 0)
+        self.opt_in_backward = (cs == "ddp" and not (cfg.optim.grad_clip > 0)
                                 and os.environ.get("B200BENCH_OPT_IN_BACKWARD", "1") != "0")
         self.seed_base = seed
         self.step_seed = torch.full((1,), seed, dtype=torch.int32, device=dev)
@@ -195,6 +198,13 @@ class NativeEngine:
         # DDP gradient buckets = the matrices of one transformer block each + (embeddings) + (vector tail)
         self._bucket_head = (0, Lt.layer_range(0)[0])
         self._bucket_tail = (Lt.layer_range(self.L - 1)[1], Lt.total)
+        # K13 bucket = this many consecutive transformer blocks per all-reduce launch (torch DDP's bucket_cap_mb,
+        # TH:217-222; 25 MiB = one tier-A block of bf16 gradients).  overlap_comm: false keeps K13 on the compute
+        # stream (DeepSpeed's knob, zero2.json:19).
+        a0_, a1_ = Lt.layer_range(0)
+        self.blocks_per_bucket = max(1, int(cfg.ddp_bucket_cap_mb * (1 << 20) // max(1, (a1_ - a0_) * 2)))
+        self.blocks_per_bucket = int(os.environ.get("B200BENCH_BLOCKS_PER_BUCKET", "0")) or self.blocks_per_bucket
+        self.overlap_comm = bool(cfg.overlap_comm)
         if ws > 1:
             torch.cuda.synchronize(dev)
             ctx.barrier()
@@ -251,6 +261,17 @@ class NativeEngine:
                 (self.L * (a1 - a0) * 2 <= 0.05 * torch.cuda.get_device_properties(dev).total_memory)
         self.keep_gathered = bool(keep) and self.param_gather == "stream"
         self.n_slots = self.L if self.keep_gathered else 2
+        # gather-ahead depth in blocks, per direction.  zero3: stage3_prefetch_bucket_size (elements, zero3.json:21)
+        # in units of one block; fsdp: forward_prefetch / backward_prefetch of the YAML (:8-10).  Bounded by the
+        # staging slots that exist (2 slots = at most one block ahead) and by 4.
+        blk = max(1, a1 - a0)
+        if self.strategy == "zero3":
+            fwd = bwd = int(self.cfg.stage3_prefetch_bucket_size // blk)
+        else:
+            fwd = 1 if self.cfg.fsdp_forward_prefetch else 0
+            bwd = 1 if self.cfg.fsdp_backward_prefetch == "backward_pre" else 0
+        cap = min(4, self.n_slots - 1)
+        self.prefetch_fwd, self.prefetch_bwd = min(fwd, cap), min(bwd, cap)
         # CTAs of one block gather: 32 are enough for tier A's 25 MB blocks (measured, profiles/README.md); big
         # blocks (403 MB at the 7B shape) need the full ~650 GB/s of a 128-CTA copy to stay ahead of the compute
         self.gather_ctas = (int(os.environ.get("B200BENCH_GATHER_CTAS", "0"))
@@ -312,9 +333,10 @@ class NativeEngine:
         if self._slot_pending[slot]:
             torch.cuda.current_stream().wait_event(self._slot_done[slot])
             self._slot_pending[slot] = False
-        nxt = l + step
-        if 0 <= nxt < self.L and self._slot_layer[nxt % self.n_slots] != nxt:
-            self._gather_block(nxt)
+        for k in range(1, (self.prefetch_fwd if step > 0 else self.prefetch_bwd) + 1):
+            nxt = l + step * k
+            if 0 <= nxt < self.L and self._slot_layer[nxt % self.n_slots] != nxt:
+                self._gather_block(nxt)
 
     def _invalidate_staging(self) -> None:
         n = getattr(self, "n_slots", 2)
@@ -409,7 +431,7 @@ class NativeEngine:
 
     def _loss_and_backward(self, first_micro: bool, last_micro: bool) -> None:
         o, P, G, p = self.ops, self.P, self.G, self.dropout
-        reduce_now = self.comm is not None and self.strategy == "ddp" and last_micro
+        reduce_now = self.comm is not None and self.comm_strategy == "ddp" and last_micro
         opt_now = self.opt_in_backward and last_micro and (self.comm is not None or self.ctx.world_size == 1)
         B, T, d, H, hd, M, V = self.B, self.T, self.d, self.H, self.hd, self.M, self.V
         acc = not first_micro
@@ -475,14 +497,19 @@ class NativeEngine:
                          G[pre + "ln_1.weight"], G[pre + "ln_1.bias"], acc)
             a, b = self.layout.layer_range(l)
             if reduce_now:
-                # K13: this block's matrix gradients are final -> all-reduce them on the comm stream
-                # while the compute stream continues with block l-1 (overlap with backward)
-                self._join_side()
-                self.comm.fork()
-                self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
-                if opt_now:
-                    with torch.cuda.stream(self.comm.stream):
-                        self._adamw_range(a, b)
+                # K13: a bucket (blocks_per_bucket consecutive blocks, contiguous in the flat buffer) is final ->
+                # all-reduce it on the comm stream while the compute stream continues with the blocks below
+                if (self.L - 1 - l) % self.blocks_per_bucket == 0:
+                    bucket_end = b
+                if (self.L - l) % self.blocks_per_bucket == 0 or l == 0:
+                    self._join_side()
+                    if self.overlap_comm:
+                        self.comm.fork()
+                    self.comm.allreduce(self.grads_pb, a, bucket_end - a, 1.0 / self.ctx.world_size,
+                                        side_stream=self.overlap_comm)
+                    if opt_now:
+                        with torch.cuda.stream(self.comm.stream if self.overlap_comm else torch.cuda.current_stream()):
+                            self._adamw_range(a, bucket_end)
             elif opt_now:
                 # single GPU: the block's wgrads were just queued on the side stream; its AdamW follows them
                 self._on_side(lambda: self._adamw_range(a, b))
@@ -490,11 +517,12 @@ class NativeEngine:
         o.embedding_bwd(self.tokens, self.dres, G["transformer.wte.weight"], G["transformer.wpe.weight"],
                         B, T, d, p, self._seed(-1, 0), accumulate_wpe=acc)
         if reduce_now:
-            self.comm.fork()
+            if self.overlap_comm:
+                self.comm.fork()
             for a, b in (self._bucket_tail, self._bucket_head):
-                self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size)
+                self.comm.allreduce(self.grads_pb, a, b - a, 1.0 / self.ctx.world_size, side_stream=self.overlap_comm)
                 if opt_now:
-                    with torch.cuda.stream(self.comm.stream):
+                    with torch.cuda.stream(self.comm.stream if self.overlap_comm else torch.cuda.current_stream()):
                         self._adamw_range(a, b)
             self.comm.join()
         elif opt_now:
@@ -555,7 +583,7 @@ class NativeEngine:
 
     def _boundary_fused(self, clip: bool) -> None:
         ctx, ws, Lt = self.ctx, self.ctx.world_size, self.layout
-        if self.strategy == "ddp":          # gradients were all-reduced and scaled during backward (K13)
+        if self.comm_strategy == "ddp":          # gradients were all-reduced and scaled during backward (K13)
             self._set_hp(1.0)
             gn = None
             if clip:
@@ -594,7 +622,7 @@ class NativeEngine:
         if self.comm is not None:
             self._boundary_fused(clip)
             return
-        if self.strategy == "ddp":
+        if self.comm_strategy == "ddp":
             if ws > 1:
                 cap = max(1, self.cfg.ddp_bucket_cap_mb * 1024 * 1024 // 2)
                 for a, b in self.layout.buckets(cap):
@@ -608,11 +636,11 @@ class NativeEngine:
         if clip:
             self.gnorm_sq.zero_()
             self.ops.sumsq(g, self.gnorm_sq, scale)
-            if self.strategy != "ddp":
+            if self.comm_strategy != "ddp":
                 ctx.all_reduce_sum(self.gnorm_sq)
             gn = self.gnorm_sq
         self.ops.adamw_flat(self.master, self.exp_avg, self.exp_avg_sq, g, self.params[self.lo:self.hi], self.hp, gn)
-        if self.strategy in SHARDED_OPT and ws > 1:
+        if self.comm_strategy in SHARDED_OPT and ws > 1:
             # zero2: all-gather updated partitions (N7); fsdp/zero3: gather before the next forward
             # (N4/N8) — with NCCL both are the same collective, issued here.
             ctx.all_gather(self.params[self.lo:self.hi], self.params)

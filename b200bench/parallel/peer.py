@@ -71,8 +71,14 @@ class PeerComm:
         self.buffers: Dict[str, PeerBuffer] = {}
         self.comm_ctas = comm_ctas
         self.use_symm = os.environ.get("B200BENCH_SYMM_MEM", "1") != "0"
-        self.use_nvls = os.environ.get("B200BENCH_NVLS", "1") != "0"
-        self.nvls_ctas = int(os.environ.get("B200BENCH_NVLS_CTAS", "0")) or 8
+        # NVLS (in-switch reduction / broadcast): from 4 ranks on by default.  At 2 ranks there is nothing to save
+        # (each rank pulls half of the bucket from its one peer either way) and the peer load/store kernel measured
+        # faster (profiles/round2/README.md).  B200BENCH_NVLS=1 / 0 forces it on / off.
+        nv = os.environ.get("B200BENCH_NVLS", "")
+        self.use_nvls = (self.ws >= 4) if nv == "" else (nv != "0")
+        self.nvls_ctas = int(os.environ.get("B200BENCH_NVLS_CTAS", "0")) or 16
+        # very large buffers (the 13 GB shards / gradients of the 7B shape) stay on cudaMalloc + IPC
+        self.symm_max_bytes = int(os.environ.get("B200BENCH_SYMM_MAX_BYTES", str(4 << 30)))
         self.flags = self.alloc("flags", int(L.b200_comm_flag_bytes()), torch.uint8)
         self.stream = torch.cuda.Stream(device=device)
         self._ev_ready = torch.cuda.Event()
@@ -85,7 +91,7 @@ class PeerComm:
         """Every rank must call this with the same arguments, in the same order."""
         nbytes = numel * torch.empty((), dtype=dtype).element_size()
         nbytes = (nbytes + 255) // 256 * 256
-        if self.use_symm:
+        if self.use_symm and nbytes <= self.symm_max_bytes:
             pb = self._alloc_symm(name, numel, nbytes, dtype)
             if pb is not None:
                 return pb

@@ -28,6 +28,17 @@ SHARDED_OPT = ("fsdp", "zero2", "zero3")
 SHARDED_PARAMS = ("fsdp", "zero3")
 
 
+def comm_strategy(strategy: str, cfg) -> str:
+    """The strategy whose partitioning / communication pattern is used.  ``--strategy fsdp`` follows the YAML's
+    ``sharding_strategy`` (reference configs/fsdp/fsdp_config.yaml:9; torch's ShardingStrategy): full_shard = own
+    pattern, shard_grad_op = ZeRO-2 (weights replicated, gradients + optimizer state partitioned), no_shard = DDP.
+    Gradient-accumulation semantics stay those of the NAMED strategy."""
+    if strategy == "fsdp":
+        return {"full_shard": "fsdp", "shard_grad_op": "zero2", "no_shard": "ddp"}[
+            getattr(cfg, "fsdp_sharding_strategy", "full_shard")]
+    return strategy
+
+
 def effective_grad_accum(strategy: str, grad_accum: int, mode: str) -> int:
     """Reference behaviour: only the DeepSpeed strategies honour ``--grad-accum``."""
     if mode == "uniform" or strategy in ("zero2", "zero3"):
@@ -40,6 +51,8 @@ class TorchEngine:
                  device: torch.device, dtype: torch.dtype, grad_accum: int = 1, dropout: float = 0.1,
                  causal: bool = False, seed: int = 42, native_ops: Optional[object] = None):
         self.strategy, self.cfg, self.ctx, self.device, self.dtype = strategy, cfg, ctx, device, dtype
+        self.comm_strategy = comm_strategy(strategy, cfg)
+        cs = self.comm_strategy
         self.accum = effective_grad_accum(strategy, grad_accum, cfg.grad_accum_mode)
         self.native_ops = native_ops
         ws, rank = ctx.world_size, ctx.rank
@@ -59,11 +72,11 @@ class TorchEngine:
         if ws > 1:                                   # N2 / N9: everyone starts from rank 0's weights
             ctx.broadcast(self.params, 0)
 
-        lo, hi = L.shard_range(rank) if strategy in SHARDED_OPT else (0, L.total)
+        lo, hi = L.shard_range(rank) if cs in SHARDED_OPT else (0, L.total)
         self.lo, self.hi = lo, hi
         self.opt = FlatAdamW(self.params[lo:hi], cfg.optim)
         self.grad_shard = (torch.zeros(hi - lo, dtype=dtype, device=device)
-                           if strategy in SHARDED_OPT else None)
+                           if cs in SHARDED_OPT else None)
         self.micro = 0
         self.params_stale = False                    # sharded-parameter strategies: needs all-gather
         self.last_grad_norm: Optional[float] = None
@@ -93,7 +106,7 @@ class TorchEngine:
 
         ws = ctx.world_size
         scale = 1.0 / ws
-        if self.strategy == "ddp":
+        if self.comm_strategy == "ddp":
             cap = max(1, self.cfg.ddp_bucket_cap_mb * 1024 * 1024 // self.grads.element_size())
             for a, b in L.buckets(cap):              # N3: reverse-order buckets
                 ctx.all_reduce_sum(self.grads[a:b])
@@ -103,16 +116,16 @@ class TorchEngine:
             g = self.grad_shard
         if self.cfg.optim.grad_clip > 0:             # global-norm clip (zero2.json:2)
             sq = (g.float() * scale).pow(2).sum()
-            if self.strategy != "ddp":
+            if self.comm_strategy != "ddp":
                 ctx.all_reduce_sum(sq)
             norm = float(sq.sqrt().item())
             self.last_grad_norm = norm
             if norm > self.cfg.optim.grad_clip:
                 scale *= self.cfg.optim.grad_clip / (norm + 1e-6)
         self.opt.step(g, self.params[self.lo:self.hi], grad_scale=scale, native=self.native_ops)
-        if self.strategy == "zero2":                 # N7: all-gather updated partitions
+        if self.comm_strategy == "zero2":                 # N7: all-gather updated partitions
             ctx.all_gather(self.params[self.lo:self.hi], self.params)
-        elif self.strategy in SHARDED_PARAMS and ws > 1:
+        elif self.comm_strategy in SHARDED_PARAMS and ws > 1:
             self.params_stale = True
         self.grads.zero_()
         return loss.detach()

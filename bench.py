@@ -127,6 +127,72 @@ def run_reference(a: argparse.Namespace) -> None:
 # ------------------------------------------------------------------------------------------
 # native arm
 # ------------------------------------------------------------------------------------------
+def run_extra(a, tier, strategy, ctx, dev, rank, local_rank, ws, steps):
+    """One more (tier, strategy) measured like the headline's device-timed arm: fresh engine, warm-up over two
+    accumulation cycles, `steps` timed steps between CUDA events, max over ranks.  Returns a dict for the
+    `strategies` object of the result line.  The shipped strategy files are used (DeepSpeed JSON for zero2 / zero3,
+    YAML for fsdp), so zero2 / zero3 accumulate over 4 micro-steps and clip like the reference's configs."""
+    import torch
+    import torch.distributed as dist
+
+    from b200bench.config import StrategyConfig, get_model_config, load_deepspeed_config, load_fsdp_config
+    from b200bench.engine import NativeEngine
+    from b200bench.utils.clocks import ClockSampler
+
+    model_cfg = get_model_config(tier, a.seq_len)
+    if strategy in ("zero2", "zero3"):
+        cfg = load_deepspeed_config(os.path.join(ROOT, "configs", "deepspeed", f"{strategy}.json"), a.batch,
+                                    GRAD_ACCUM, ws)
+    elif strategy == "fsdp":
+        cfg = load_fsdp_config(os.path.join(ROOT, "configs", "fsdp", "fsdp_config.yaml"))
+    else:
+        cfg = StrategyConfig()
+    torch.cuda.reset_peak_memory_stats(dev)
+    eng = NativeEngine(model_cfg, strategy, cfg, ctx, dev, grad_accum=GRAD_ACCUM, dropout=a.dropout, causal=False,
+                       batch=a.batch, seq_len=a.seq_len, comm=a.comm, use_graph=not a.no_graph)
+    try:
+        gen = torch.Generator(device="cpu").manual_seed(1234 + rank)
+        toks = [torch.randint(0, model_cfg["vocab_size"], (a.batch, a.seq_len), generator=gen, dtype=torch.int32).to(dev)
+                for _ in range(4)]
+
+        def sync_all():
+            torch.cuda.synchronize(dev)
+            if ws > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+
+        n_warm = max(3, 2 * eng.accum + 2 if eng.accum > 1 else 3)
+        n_warm += (-n_warm) % eng.accum
+        steps += (-steps) % eng.accum                     # whole accumulation cycles
+        for i in range(n_warm):
+            eng.train_step(toks[i % 4], toks[i % 4])
+        sync_all()
+        sampler = ClockSampler(local_rank).start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            loss = eng.train_step(toks[i % 4], toks[i % 4])
+        e1.record()
+        sync_all()
+        clocks = sampler.stop()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if ws > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        peak = torch.cuda.max_memory_allocated(dev) + eng.extra_memory_bytes()
+        out = {"tier": tier, "value": a.batch * a.seq_len * ws * steps / (ms / 1e3), "unit": "tokens/s",
+               "ms_per_step": ms / steps, "steps": steps, "warmup": n_warm, "grad_accum": eng.accum,
+               "peak_vram_gb": peak / 1e9, "final_loss": float(loss[0]),
+               "param_gather": eng.param_gather if getattr(eng, "sharded_params", False) else None,
+               "params_m": round(eng.layout.num_params() / 1e6, 1),
+               "clocks": {"sm_mhz": clocks.get("sm_mhz"), "reasons": clocks.get("reasons")}}
+    finally:
+        eng.close()
+        del eng
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_native(a: argparse.Namespace) -> None:
     import torch
     import torch.distributed as dist
@@ -206,9 +272,10 @@ def run_native(a: argparse.Namespace) -> None:
     value = tokens / (dev_ms / 1e3)
     e2e_value = tokens / (e2e_ms / 1e3)
     peak = torch.cuda.max_memory_allocated(dev) + eng.extra_memory_bytes()
+    result = None
     if rank == 0:
         per_step = eng.kernel_launches_per_step()
-        emit({
+        result = ({
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": ws, "steps": a.steps,
             "warmup": n_warm, "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": (value / PUBLISHED_DDP[ws]) if ws in PUBLISHED_DDP else None,
@@ -238,6 +305,34 @@ def run_native(a: argparse.Namespace) -> None:
         phases = eng.profile_breakdown() if eng.accum == 1 else {}
         print(f"[diag] rank {rank}: host enqueue {host_ms:.3f} ms/step, phases {phases}", file=sys.stderr, flush=True)
     eng.close()
+    del eng
+    torch.cuda.empty_cache()
+    # ---- the other strategies of the reference's matrix (scripts/run_all_benchmarks.sh:32-52 there), same box,
+    # same launch, in the SAME result line under "strategies"; the headline above stays ddp.  A failing extra is
+    # recorded as {"error": ...} and never costs the headline.
+    extras = {}
+    if a.extras and a.strategy == "ddp":
+        todo = [(a.tier, "zero2"), (a.tier, "fsdp"), (a.tier, "zero3")]
+        if ws >= 2 and os.environ.get("B200BENCH_BENCH_7B", "1") != "0":
+            todo.append(("7B", "zero3"))
+        for tier, strat in todo:
+            key = strat if tier == a.tier else f"{strat}_{tier}"
+            ok = 1
+            try:
+                extras[key] = run_extra(a, tier, strat, ctx, dev, rank, local_rank, ws, min(a.steps, 12))
+            except Exception as e:      # noqa: BLE001
+                extras[key] = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
+                ok = 0
+            if ws > 1:                  # ranks agree whether to go on (a rank that failed may have left a collective)
+                flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                ok = int(flag.item())
+            if not ok:
+                extras.setdefault(key, {})["aborted_remaining"] = True
+                break
+    if rank == 0:
+        result["strategies"] = extras
+        emit(result)
     if ws > 1:
         dist.destroy_process_group()
 
@@ -256,6 +351,8 @@ def main() -> None:
     ap.add_argument("--dropout", type=float, default=0.1)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--diag", action="store_true", help="after the timed arms, print a per-phase breakdown to stderr")
+    ap.add_argument("--no-extras", dest="extras", action="store_false",
+                    help="headline only: skip the zero2 / fsdp / zero3 (and 7B zero3) runs reported under 'strategies'")
     ap.add_argument("--ref-timeout", type=float, default=180.0, help="seconds before the reference arm is abandoned")
     a = ap.parse_args()
     quiet_stdout()

@@ -10,10 +10,10 @@ run() {  # name, extra env, args...
   PORT=$((PORT + 1))
   local out
   if [ "$N" -gt 1 ]; then
-    out=$(env $envs timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" --master-addr 127.0.0.1 \
-          --master-port "$PORT" bench.py --gpus "$N" --steps "$STEPS" --warmup 5 "$@" 2>/dev/null | tail -1)
+    out=$(env $envs timeout 120 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" --master-addr 127.0.0.1 \
+          --master-port "$PORT" bench.py --gpus "$N" --steps "$STEPS" --warmup 5 --no-extras "$@" 2>/dev/null | tail -1)
   else
-    out=$(env $envs timeout 300 python bench.py --gpus 1 --steps "$STEPS" --warmup 5 "$@" 2>/dev/null | tail -1)
+    out=$(env $envs timeout 120 python bench.py --gpus 1 --steps "$STEPS" --warmup 5 --no-extras "$@" 2>/dev/null | tail -1)
   fi
   python - "$name" "$out" <<'PY'
 import json, sys

@@ -69,12 +69,17 @@ def main():
     dist.all_reduce(ref)
     ref /= ws
     off, cnt = 128, n - 256
-    comm.allreduce(gb, off, cnt, 1.0 / ws, side_stream=False)
-    torch.cuda.synchronize(dev)
-    got = gb.tensor.float()
-    err = (got[off:off + cnt] - ref[off:off + cnt]).abs().max().item()
-    untouched = torch.equal(gb.tensor[:off], src[:off]) and torch.equal(gb.tensor[off + cnt:], src[off + cnt:])
-    report("K13 allreduce_scale", err < 0.02 and untouched, f"max_err={err:.4f}")
+    nvls_default = comm.use_nvls
+    for mode in (["p2p", "nvls"] if gb.mc_ptr else ["p2p"]):       # both data paths, whatever the default is
+        comm.use_nvls = mode == "nvls"
+        gb.tensor.copy_(src)
+        comm.allreduce(gb, off, cnt, 1.0 / ws, side_stream=False)
+        torch.cuda.synchronize(dev)
+        got = gb.tensor.float()
+        err = (got[off:off + cnt] - ref[off:off + cnt]).abs().max().item()
+        untouched = torch.equal(gb.tensor[:off], src[:off]) and torch.equal(gb.tensor[off + cnt:], src[off + cnt:])
+        report(f"K13 allreduce_scale ({mode})", err < 0.02 and untouched, f"max_err={err:.4f}")
+    comm.use_nvls = nvls_default
     # second launch (epoch advance) on the side stream with fork/join
     gb.tensor.copy_(src)
     comm.fork(); comm.allreduce(gb, 0, n, 1.0 / ws); comm.join()
@@ -174,7 +179,7 @@ def main():
                         continue
                     comm.use_nvls = mode == "nvls"
                     res[mode] = timed(lambda: comm.allreduce(big, 0, cnt, 1.0 / ws, side_stream=False), 10, ws, dev)
-                comm.use_nvls = True
+                comm.use_nvls = nvls_default
                 if rank == 0:
                     txt = "  ".join(f"{k} {v*1e3:8.1f} us (busbw {2 * (ws - 1) / ws * cnt * 2 / v / 1e6:5.0f} GB/s)"
                                     for k, v in res.items())

@@ -120,3 +120,64 @@ def test_engine_knobs_come_from_the_strategy_files(tmp_path):
     f = load_fsdp_config(os.path.join(ROOT, "configs", "fsdp", "fsdp_config.yaml"))
     assert f.param_gather == "stream" and f.gather_ctas == 0
     assert StrategyConfig().param_gather is None                      # plain ddp: engine default
+
+
+# ---- round 2: every key of a strategy file is applied, pinned to its one supported value, or rejected ----------
+def test_strategy_files_reject_what_would_be_ignored(tmp_path):
+    import json
+
+    import yaml
+
+    from b200bench.config import load_deepspeed_config, load_fsdp_config
+
+    ref = "/root/reference/configs"
+    if os.path.isdir(ref):                      # the reference's own files load unchanged
+        for n in ("zero2", "zero3"):
+            load_deepspeed_config(f"{ref}/deepspeed/{n}.json", 1, 4, 8)
+        f = load_fsdp_config(f"{ref}/fsdp/fsdp_config.yaml")
+        assert f.fsdp_sharding_strategy == "full_shard" and len(f.notes) == 2      # size_based, mixed_precision: false
+    raw = json.load(open(os.path.join(ROOT, "configs", "deepspeed", "zero3.json")))
+
+    def ds(mut):
+        r = json.loads(json.dumps(raw))
+        mut(r)
+        p = tmp_path / "z.json"
+        p.write_text(json.dumps(r))
+        return load_deepspeed_config(str(p), 1, 4, 8)
+
+    with pytest.raises(ValueError, match="contiguous_gradients"):
+        ds(lambda r: r["zero_optimization"].update(contiguous_gradients=False))
+    with pytest.raises(ValueError, match="not supported"):
+        ds(lambda r: r["zero_optimization"].update(zero_hpz_partition_size=2))
+    with pytest.raises(ValueError, match="not supported"):
+        ds(lambda r: r.update(activation_checkpointing={"partition_activations": True}))
+    with pytest.raises(ValueError, match="bf16"):
+        ds(lambda r: r["bf16"].update(enabled=False))
+    with pytest.raises(ValueError, match="stage"):
+        ds(lambda r: r["zero_optimization"].update(stage=1))
+    c = ds(lambda r: r["zero_optimization"].update(overlap_comm=False, stage3_prefetch_bucket_size=2.6e7))
+    assert c.overlap_comm is False and c.stage3_prefetch_bucket_size == 26000000
+
+    def fs(**kw):
+        p = tmp_path / "f.yaml"
+        p.write_text(yaml.safe_dump({"fsdp_config": kw}))
+        return load_fsdp_config(str(p))
+
+    assert fs(sharding_strategy="SHARD_GRAD_OP").fsdp_sharding_strategy == "shard_grad_op"
+    assert fs(backward_prefetch="BACKWARD_POST", forward_prefetch=False).fsdp_forward_prefetch is False
+    for bad in (dict(sharding_strategy="hybrid_shard"), dict(backward_prefetch="sometimes"), dict(use_orig_params=True),
+                dict(mixed_precision="fp16"), dict(auto_wrap_policy="by_name")):
+        with pytest.raises(ValueError):
+            fs(**bad)
+
+
+def test_fsdp_sharding_strategy_selects_the_communication_pattern():
+    from b200bench.config import StrategyConfig
+    from b200bench.parallel.torch_engine import comm_strategy
+
+    c = StrategyConfig()
+    assert comm_strategy("fsdp", c) == "fsdp" and comm_strategy("zero3", c) == "zero3"
+    c.fsdp_sharding_strategy = "shard_grad_op"
+    assert comm_strategy("fsdp", c) == "zero2" and comm_strategy("ddp", c) == "ddp"
+    c.fsdp_sharding_strategy = "no_shard"
+    assert comm_strategy("fsdp", c) == "ddp"
