@@ -105,6 +105,8 @@ class NativeOps:
              rowdot=None, rd_T=0, rd_hd=0, peer=None, mc_units=0) -> None:
         """``peer`` (K14): dict(table=<c_void_p array of the owners' shard bases>, ws, flat_off, shard) - B is then
         fetched tile by tile from the owning ranks and the ``B`` argument is only used for its shape."""
+        if peer is not None and mc_units > 1:
+            raise NativeError("cluster multicast is for a local B only: TMA multicast loads read only this GPU's memory")
         lda = lda or (M if a_mn else K)
         ldb = ldb or (N if b_mn else K)
         ldd = ldd or N

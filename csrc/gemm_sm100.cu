@@ -22,11 +22,11 @@
 // when B is a weight matrix that is partitioned over ranks, there is one tensor map per OWNING rank over
 // that rank's shard as mapped into this process (peer memory over NVLink), and every B tile is fetched by
 // TMA straight from its owner into shared memory - no gather pass, no staging copy in HBM, no flags.
-// The kernel can also share B inside a thread-block cluster: the CTAs (or CTA pairs) that work on the same N-tile
-// for different M-tiles each fetch 1/P of the B tile and multicast it to the others (.multicast::cluster).  That
-// is meant for exactly the remote case (peer data is not cached by the local L2, so every CTA that needs a tile
-// pulls it over NVLink again), but multicast loads FROM peer memory are switched off - see gemm_impl - so today it
-// only serves a local B.
+// For a LOCAL B the kernel can also share B inside a thread-block cluster: the CTAs (or CTA pairs) that work on the
+// same N-tile for different M-tiles each fetch 1/P of the B tile and multicast it to the others
+// (.multicast::cluster).  TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load
+// from another GPU's memory hung the GPU: a partitioned B is fetched unicast by every CTA (host and kernel both
+// refuse the combination).
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -126,6 +126,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   using Cfg = GemmCfg<BN, CTAS>;
   constexpr int BNL = Cfg::kBNLocal;
   const int P = p.units;
+  if (P > 1 && p.b_ws > 1) __trap();   // multicast loads only from local memory (see the header comment); never reached
   const int CL = P * CTAS;                                  // CTAs per cluster
   const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
   const uint32_t cta_rank = crank % CTAS;                   // which half of a pair
@@ -817,11 +818,8 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   const int b_rows = b_mn ? K : N;      // rows of the stored weight matrix
   // bn_hint: 0 = auto, 128 / 256 = single-CTA tile width, 2128 / 2256 = CTA-pair (cta_group::2) mode
   int BN = bn_hint % 1000, CTAS = bn_hint >= 2000 ? 2 : 1;
-  // Cluster multicast of B is only used for a LOCAL B.  On this driver (580.159, B200) a TMA multicast load whose
-  // source is peer memory (cp.async.bulk.tensor ... .multicast::cluster from an NVLink-mapped address) stopped the
-  // GPU outright in two separate 2-GPU runs - no trap, no Xid the process could see, the device just went away -
-  // while the same kernel is correct with unicast TMA from peers (tests/multi/check_k14.py) and with multicast
-  // from local memory (tests/test_kernels_gpu.py).  So a partitioned B is always fetched unicast, per CTA.
+  // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+  // memory hung the GPU.  A partitioned B (tensor maps over peer memory) is therefore always fetched unicast.
   if (b_ws > 1 && ex && ex->mc_units > 1) return -2;
   int want_units = (b_ws > 1) ? 1 : (ex ? ex->mc_units : 0);   // 0 = auto = off
   // Units per cluster for a (bn, ctas) candidate: as many consecutive M-tiles as there are (<= 8, power of two),

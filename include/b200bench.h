@@ -201,8 +201,8 @@ int b200_set_gemm_pdl(int on);
  *                        SURVEY N4,N8).  Returns -9 when no tile shape keeps every TMA box inside one owner.
  *  mc_units              tile units (CTAs / CTA pairs along M) per thread-block cluster that share each B tile by
  *                        TMA multicast: 0 / 1 = off, 2 / 4 / 8 = that many.  Local B only: with a partitioned B
- *                        (b_ws > 1) any value > 1 is rejected (-2) - multicast TMA loads from peer memory took
- *                        the GPU down on driver 580.159, see csrc/gemm_sm100.cu. */
+ *                        (b_ws > 1) any value > 1 is rejected (-2).  TMA multicast loads here read only this GPU's
+ *                        memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU. */
 typedef struct B200GemmEx {
   void* dbias;
   int dbias_accum;
