@@ -646,6 +646,10 @@ class NativeEngine:
             ctx.all_gather(self.params[self.lo:self.hi], self.params)
 
     def train_step(self, tokens: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        # the library keeps ONE per-step dropout seed word; with several engines alive in a process (tests build many)
+        # each step points it at THIS engine's word, so eager launches never advance another engine's masks (a
+        # captured graph has the pointer baked in at capture time, which is the same word)
+        self.ops.step_seed_register(self.step_seed)
         self.tokens.copy_(tokens, non_blocking=True)
         if targets is tokens:
             self.targets.copy_(self.tokens, non_blocking=True)
@@ -670,6 +674,8 @@ class NativeEngine:
         graph and replayed ``reps`` times between CUDA events, so the numbers carry no Python launch
         overhead.  Call between training steps on an accumulation boundary; the replays are real work
         (weights move by ``reps`` optimizer steps) and ranks must call it together."""
+        self.ops.step_seed_register(self.step_seed)
+
         def timed(fn) -> float:
             fn()                                      # warm (also keeps lazy init out of the capture)
             torch.cuda.synchronize(self.device)
@@ -754,6 +760,8 @@ class NativeEngine:
 
     def close(self) -> None:
         self._graphs.clear()
+        if getattr(self.ops, "_seed_word", None) is self.step_seed:
+            self.ops.step_seed_unregister()       # the library must not keep pointing at a closed engine's word
         if self.comm is not None:
             self.P, self.G = {}, {}
             self.grads = self.params = None

@@ -45,6 +45,9 @@ def load_strategy_config(args: Any) -> StrategyConfig:
     else:
         cfg = StrategyConfig()
     cfg.grad_accum_mode = getattr(args, "grad_accum_mode", "reference")
+    if cfg.notes and getattr(args, "rank", 0) == 0:
+        for n in cfg.notes:                     # values of a strategy file that were read as something else
+            print(f"NOTE ({args.strategy} config): {n}")
     return cfg
 
 

@@ -272,6 +272,10 @@ class NativeOps:
         self._seed_word = word          # keep the tensor alive for as long as the library points at it
         self._ck(self.lib.b200_step_seed_register(_p(word)), "step_seed_register")
 
+    def step_seed_unregister(self) -> None:
+        self._seed_word = None
+        self._ck(self.lib.b200_step_seed_register(c_void_p(0)), "step_seed_unregister")
+
     def step_seed_advance(self) -> None:
         self._ck(self.lib.b200_step_seed_advance(_stream()), "step_seed_advance")
         self.launches += 1

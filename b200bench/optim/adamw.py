@@ -9,7 +9,8 @@ configured by ``configs/deepspeed/zero2.json:27-35``; ``WarmupLR`` follows
 log, the reference sets no ``warmup_type`` so the log ramp is reproduced when ``log=True``).
 
 The torch implementation here is the oracle and the CPU path; on a GPU the same update runs as
-one fused kernel (``csrc/adamw.cu``) through ``b200bench.ops``.
+one fused kernel (``adamw_kernel`` in ``csrc/elementwise.cu``; fused with the gradient reduce-scatter as K15 in
+``csrc/comm.cu``) through ``b200bench.ops``.
 """
 from __future__ import annotations
 

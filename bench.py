@@ -66,6 +66,9 @@ def emit(obj: dict) -> None:
 def run_reference(a: argparse.Namespace) -> None:
     rank, local_rank, ws = env_int("RANK", 0), env_int("LOCAL_RANK", 0), env_int("WORLD_SIZE", 1)
     harness = os.path.join(ROOT, "baseline", "_ref", "benchmarking", "train_harness.py")
+    if not os.path.exists(harness) and os.path.isdir("/root/reference") and rank == 0:
+        subprocess.run(["bash", os.path.join(ROOT, "baseline", "install_reference.sh")], check=False,
+                       capture_output=True)       # git-ignored directory: re-create it from the read-only reference
     if not os.path.exists(harness):
         if rank == 0:
             emit({"impl": "reference", "unavailable": "baseline/_ref missing: run baseline/install_reference.sh"})

@@ -89,10 +89,10 @@ __device__ __forceinline__ void rank_barrier(const PeerPtrs& flags, int rank, in
     uint64_t t0 = 0;
     while (static_cast<int32_t>(ld_acquire_sys(src) - value) < 0) {
       bool expired = false;
-      if ((++spins & 255u) == 0) {       // wall-clock bound (20 s: ranks may reach a collective seconds apart)
+      if ((++spins & 255u) == 0) {       // wall-clock bound (60 s: ranks may reach a collective seconds apart)
         const uint64_t now = global_timer_ns();
         if (t0 == 0) t0 = now;
-        expired = now - t0 > 5 * kWaitTimeoutNs;
+        expired = now - t0 > 15 * kWaitTimeoutNs;
       }
       if (expired) {  // a peer never arrived: abort instead of hanging
 #ifdef B200_COMM_DEBUG
@@ -119,7 +119,7 @@ __device__ __forceinline__ void grid_barrier(uint32_t* ctr, uint32_t target) {
       if ((++spins & 255u) == 0) {
         const uint64_t now = global_timer_ns();
         if (t0 == 0) t0 = now;
-        expired = now - t0 > 5 * kWaitTimeoutNs;
+        expired = now - t0 > 15 * kWaitTimeoutNs;
       }
       if (expired) {
 #ifdef B200_COMM_DEBUG
@@ -305,8 +305,8 @@ __device__ __forceinline__ void adam8(float* master, float* m, float* v, size_t 
     const float gj = g[j] * gscale;
     mm[j] = b1 * mm[j] + (1.f - b1) * gj;
     vv[j] = b2 * vv[j] + (1.f - b2) * gj * gj;
-    const float denom = sqrtf(vv[j]) * isbc2 + eps;
-    w[j] = w[j] * (1.f - lr * wd) - lr * ibc1 * mm[j] / denom;
+    const float denom = __fsqrt_rn(vv[j]) * isbc2 + eps;       // IEEE sqrt / div: see adam_update4 (elementwise.cu)
+    w[j] = w[j] * (1.f - lr * wd) - __fdiv_rn(lr * ibc1 * mm[j], denom);
     wout[j] = w[j];
   }
   wp[0] = w4[0]; wp[1] = w4[1];

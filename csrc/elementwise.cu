@@ -722,8 +722,10 @@ __device__ __forceinline__ void adam_update4(float4& w, float4& m, float4& v, co
     const float gj = g[j] * c.gscale;
     mp[j] = c.b1 * mp[j] + (1.f - c.b1) * gj;
     vp[j] = c.b2 * vp[j] + (1.f - c.b2) * gj * gj;
-    const float denom = sqrtf(vp[j]) * c.isbc2 + c.eps;
-    wp[j] = wp[j] * (1.f - c.lr * c.wd) - c.lr * c.ibc1 * mp[j] / denom;
+    // IEEE square root and division (round-to-nearest intrinsics are not affected by --use_fast_math), so the
+    // update stays comparable with torch.optim.AdamW to fp32 rounding
+    const float denom = __fsqrt_rn(vp[j]) * c.isbc2 + c.eps;
+    wp[j] = wp[j] * (1.f - c.lr * c.wd) - __fdiv_rn(c.lr * c.ibc1 * mp[j], denom);
   }
 }
 
