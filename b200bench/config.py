@@ -58,7 +58,7 @@ class StrategyConfig:
     allgather_bucket_size: int = int(5e8)
     overlap_comm: bool = True
     # DDP bucket cap in MiB (torch DDP default 25)
-    ddp_bucket_cap_mb: int = 50      # two tier-A blocks of bf16 gradients per K13 launch (measured best at 2 GPUs)
+    ddp_bucket_cap_mb: int = 0       # 0 = engine default (see NativeEngine.blocks_per_bucket); torch DDP's default is 25
     # ZeRO-3 knobs (``zero3.json:20-26``)
     stage3_prefetch_bucket_size: int = int(5e8)
     stage3_param_persistence_threshold: int = int(1e5)

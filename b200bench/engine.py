@@ -202,7 +202,12 @@ class NativeEngine:
         # TH:217-222; 25 MiB = one tier-A block of bf16 gradients).  overlap_comm: false keeps K13 on the compute
         # stream (DeepSpeed's knob, zero2.json:19).
         a0_, a1_ = Lt.layer_range(0)
-        self.blocks_per_bucket = max(1, int(cfg.ddp_bucket_cap_mb * (1 << 20) // max(1, (a1_ - a0_) * 2)))
+        if cfg.ddp_bucket_cap_mb > 0:
+            self.blocks_per_bucket = max(1, int(cfg.ddp_bucket_cap_mb * (1 << 20) // max(1, (a1_ - a0_) * 2)))
+        else:
+            # measured (profiles/round2): the in-switch all-reduce (>= 4 ranks) is best launched per block (8 GPUs:
+            # 8.89 vs 9.03 ms per step); the peer load/store kernel at 2 ranks per two blocks (9.00 vs 9.19 ms)
+            self.blocks_per_bucket = 1 if (self.comm is not None and self.comm.use_nvls) else 2
         self.blocks_per_bucket = int(os.environ.get("B200BENCH_BLOCKS_PER_BUCKET", "0")) or self.blocks_per_bucket
         self.overlap_comm = bool(cfg.overlap_comm)
         if ws > 1:
@@ -624,7 +629,7 @@ class NativeEngine:
             return
         if self.comm_strategy == "ddp":
             if ws > 1:
-                cap = max(1, self.cfg.ddp_bucket_cap_mb * 1024 * 1024 // 2)
+                cap = max(1, (self.cfg.ddp_bucket_cap_mb or 25) * 1024 * 1024 // 2)
                 for a, b in self.layout.buckets(cap):
                     ctx.all_reduce_sum(self.grads[a:b])
             g = self.grads

@@ -65,6 +65,8 @@ class PeerComm:
         L.b200_comm_allreduce.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
         L.b200_comm_rs_adamw.argtypes = [vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
         L.b200_comm_gather_range.argtypes = [vp, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_ulonglong, i, vp]
+        L.b200_comm_gather_range_from.argtypes = [vp, i, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong,
+                                                  ctypes.c_ulonglong, i, vp]
         L.b200_comm_allreduce_nvls.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
         L.b200_comm_rs_adamw_nvls.argtypes = [vp, vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
         L.b200_peer_copy.argtypes = [vp, vp, sz, i, vp]
@@ -208,8 +210,8 @@ class PeerComm:
         return (c_void_p * self.ws)(*[pp - r * shard_elems * elem_size for r, pp in enumerate(buf.peer_ptrs)])
 
     def gather_range(self, table, dst: torch.Tensor, flat_off: int, n: int, shard_elems: int, ctas: int = 128) -> None:
-        rc = self.ops.lib.b200_comm_gather_range(table, self.ws, c_void_p(dst.data_ptr()), flat_off, n,
-                                                 shard_elems, ctas,
+        rc = self.ops.lib.b200_comm_gather_range_from(table, self.ws, self.rank, c_void_p(dst.data_ptr()), flat_off, n,
+                                                      shard_elems, ctas,
                                                  c_void_p(torch.cuda.current_stream().cuda_stream))
         if rc:
             raise _ops.NativeError(f"comm_gather_range failed with code {rc}")

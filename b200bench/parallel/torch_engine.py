@@ -107,7 +107,7 @@ class TorchEngine:
         ws = ctx.world_size
         scale = 1.0 / ws
         if self.comm_strategy == "ddp":
-            cap = max(1, self.cfg.ddp_bucket_cap_mb * 1024 * 1024 // self.grads.element_size())
+            cap = max(1, (self.cfg.ddp_bucket_cap_mb or 25) * 1024 * 1024 // self.grads.element_size())
             for a, b in L.buckets(cap):              # N3: reverse-order buckets
                 ctx.all_reduce_sum(self.grads[a:b])
             g = self.grads

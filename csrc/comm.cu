@@ -508,7 +508,7 @@ peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t 
 // their GEMMs instead, see gemm_sm100.cu K14).  src[r] is rank r's partition base minus r*shard.
 __global__ void __launch_bounds__(COMM_THREADS, 2)
 gather_range_kernel(PeerPtrs src, __nv_bfloat16* __restrict__ dst, unsigned long long flat_off,
-                    unsigned long long n, unsigned long long shard) {
+                    unsigned long long n, unsigned long long shard, unsigned long long rot) {
   constexpr int U = 8;   // 16-byte loads in flight per thread (NVLink round trip ~2.5 us)
   const size_t nvec = n >> 3;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
@@ -518,11 +518,16 @@ gather_range_kernel(PeerPtrs src, __nv_bfloat16* __restrict__ dst, unsigned long
   const uint32_t shard_vec = static_cast<uint32_t>(shard >> 3);
   for (size_t i0 = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += U * stride) {
     uint4 v[U];
+    // Every rank gathers the same range at the same time.  Walking it from the start would have all of them read
+    // the same owner at once (one GPU's NVLink egress shared by N-1 readers: 110 GB/s per reader at 8 GPUs, measured);
+    // each rank starts `rot` vectors into the range instead, so at any moment the readers are spread over the owners.
+    size_t idx[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const size_t i = i0 + u * stride;
+      idx[u] = i + rot < nvec ? i + rot : i + rot - nvec;
       if (i < nvec) {
-        const uint32_t fv = vec0 + static_cast<uint32_t>(i);
+        const uint32_t fv = vec0 + static_cast<uint32_t>(idx[u]);
         const int owner = static_cast<int>(fv / shard_vec);
         v[u] = ld_peer_v4(static_cast<const __nv_bfloat16*>(src.p[owner]) + static_cast<size_t>(fv) * 8);
       }
@@ -530,7 +535,7 @@ gather_range_kernel(PeerPtrs src, __nv_bfloat16* __restrict__ dst, unsigned long
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const size_t i = i0 + u * stride;
-      if (i < nvec) reinterpret_cast<uint4*>(dst)[i] = v[u];
+      if (i < nvec) reinterpret_cast<uint4*>(dst)[idx[u]] = v[u];
     }
   }
 }
@@ -745,10 +750,17 @@ extern "C" int b200_comm_rs_adamw_loop(void* const* grads, void* const* weights,
 extern "C" int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst,
                                       unsigned long long flat_off, unsigned long long n,
                                       unsigned long long shard_elems, int ctas, void* stream) {
+  return b200_comm_gather_range_from(shard_adj, ws, 0, dst, flat_off, n, shard_elems, ctas, stream);
+}
+
+extern "C" int b200_comm_gather_range_from(void* const* shard_adj, int ws, int rank, void* dst,
+                                           unsigned long long flat_off, unsigned long long n,
+                                           unsigned long long shard_elems, int ctas, void* stream) {
   if (n % 8 || flat_off % 8 || shard_elems % 8 || ws > MAX_RANKS) return -2;
   if (((flat_off + n) >> 3) > 0xFFFFFFFFull || (shard_elems >> 3) > 0xFFFFFFFFull || shard_elems == 0) return -3;
   gather_range_kernel<<<ctas > 0 ? ctas : 128, COMM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      make_ptrs(shard_adj, ws), static_cast<__nv_bfloat16*>(dst), flat_off, n, shard_elems);
+      make_ptrs(shard_adj, ws), static_cast<__nv_bfloat16*>(dst), flat_off, n, shard_elems,
+      ws > 0 ? (n >> 3) * static_cast<unsigned long long>(rank < 0 ? 0 : rank % ws) / ws : 0ull);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -219,7 +219,11 @@ int b200_gemm_bf16_ex(const void* A, const void* B, void* D, int M, int N, int K
                       const B200GemmEx* ex);
 /* Encoded TMA descriptors are cached by (address, shape, box); counters for tests and diagnostics. */
 int b200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
-/* Plain gather of the flat range [flat_off, flat_off+n) from the owners' partitions into dst. */
+/* Plain gather of the flat range [flat_off, flat_off+n) from the owners' partitions into dst.  The _from variant
+ * takes the calling rank and starts rank/ws of the way into the range (wrapping around), so that ranks that gather
+ * the same range at the same time read different owners at any moment instead of all hitting one GPU's links. */
+int b200_comm_gather_range_from(void* const* shard_adj, int ws, int rank, void* dst, unsigned long long flat_off,
+                                unsigned long long n, unsigned long long shard_elems, int ctas, void* stream);
 int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst, unsigned long long flat_off,
                            unsigned long long n, unsigned long long shard_elems, int ctas,
                            void* stream);
