@@ -20,6 +20,8 @@ def _lib(native):
     L.b200_comm_allreduce_loop.argtypes = [vp, vp, i, sz, sz, f, i, vp]
     L.b200_comm_rs_adamw_loop.argtypes = [vp, vp, vp, i, vp, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
     L.b200_comm_gather_range.argtypes = [vp, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_ulonglong, i, vp]
+    L.b200_comm_gather_range_from.argtypes = [vp, i, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong,
+                                              ctypes.c_ulonglong, i, vp]
     return L
 
 
@@ -140,3 +142,9 @@ def test_gather_range_single_process(native):
     rc = L.b200_comm_gather_range(adj, ws, c_void_p(dst.data_ptr()), off, n, shard, 8, _stream())
     assert rc == 0
     assert torch.equal(dst, full[off:off + n])
+    for rank in range(ws):                       # each rank starts at a different owner and wraps around
+        for n2 in (n, 8 * 1201, 8 * 3):
+            dst = torch.zeros(n2, dtype=BF16, device=DEV)
+            rc = L.b200_comm_gather_range_from(adj, ws, rank, c_void_p(dst.data_ptr()), off, n2, shard, 3, _stream())
+            assert rc == 0
+            assert torch.equal(dst, full[off:off + n2]), (rank, n2)
