@@ -314,28 +314,50 @@ def run_native(a: argparse.Namespace) -> None:
     # same launch, in the SAME result line under "strategies"; the headline above stays ddp.  A failing extra is
     # recorded as {"error": ...} and never costs the headline.
     extras = {}
-    if a.extras and a.strategy == "ddp":
-        todo = [(a.tier, "zero2"), (a.tier, "fsdp"), (a.tier, "zero3")]
-        if ws >= 2 and os.environ.get("B200BENCH_BENCH_7B", "1") != "0":
-            todo.append(("7B", "zero3"))
-        for tier, strat in todo:
-            key = strat if tier == a.tier else f"{strat}_{tier}"
-            ok = 1
-            try:
-                extras[key] = run_extra(a, tier, strat, ctx, dev, rank, local_rank, ws, min(a.steps, 12))
-            except Exception as e:      # noqa: BLE001
-                extras[key] = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
-                ok = 0
-            if ws > 1:                  # ranks agree whether to go on (a rank that failed may have left a collective)
-                flag = torch.tensor([ok], dtype=torch.int32, device=dev)
-                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-                ok = int(flag.item())
-            if not ok:
-                extras.setdefault(key, {})["aborted_remaining"] = True
-                break
-    if rank == 0:
-        result["strategies"] = extras
-        emit(result)
+    if rank == 0 and ws > 1 and a.extras:
+        # torchrun sends SIGTERM to the surviving ranks when one rank of an extra dies, and this rank may sit in a
+        # blocking CUDA / NCCL call at that moment: the C-level handler writes to a wake-up pipe, a watcher thread
+        # prints the headline (with the extras finished so far) and exits.
+        import signal
+        import threading
+        r_fd, w_fd = os.pipe()
+        os.set_blocking(w_fd, False)
+        signal.signal(signal.SIGTERM, lambda signum, frame: None)
+        signal.set_wakeup_fd(w_fd, warn_on_full_buffer=False)
+
+        def _watch():
+            os.read(r_fd, 1)
+            extras["aborted"] = "signal from the launcher (another rank exited)"
+            result["strategies"] = extras
+            emit(result)
+            os._exit(0)
+        threading.Thread(target=_watch, daemon=True).start()
+    try:
+        if a.extras and a.strategy == "ddp":
+            todo = [(a.tier, "zero2"), (a.tier, "fsdp"), (a.tier, "zero3")]
+            if ws >= 2 and os.environ.get("B200BENCH_BENCH_7B", "1") != "0":
+                todo.append(("7B", "zero3"))
+            for tier, strat in todo:
+                key = strat if tier == a.tier else f"{strat}_{tier}"
+                ok = 1
+                try:
+                    extras[key] = run_extra(a, tier, strat, ctx, dev, rank, local_rank, ws, min(a.steps, 12))
+                except Exception as e:      # noqa: BLE001
+                    extras[key] = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
+                    ok = 0
+                if ws > 1:              # ranks agree whether to go on (a rank that failed may have left a collective)
+                    flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                    ok = int(flag.item())
+                if not ok:
+                    extras.setdefault(key, {})["aborted_remaining"] = True
+                    break
+    except BaseException as e:          # noqa: BLE001  (a dead CUDA context after a failed extra: keep the headline)
+        extras["aborted"] = f"{type(e).__name__}: {str(e)[:200]}"
+    finally:
+        if rank == 0:
+            result["strategies"] = extras
+            emit(result)
     if ws > 1:
         dist.destroy_process_group()
 

@@ -20,6 +20,7 @@ except Exception as e:
     print("bench parse failed", e)
 PY
 tail -3 gpurun_out/n$N/bench.err
+[ "${VARIANTS:-1}" = 1 ] || exit 0
 source /dev/stdin <<'EOS'
 run(){ PORT=$((29700 + RANDOM % 200)); env "$@" timeout 120 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT bench.py --gpus $N --steps 20 --warmup 5 --no-extras 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('%-60s %.3f ms' % (sys.argv[1], d['ms_per_step']))" "$*"; }
 EOS
