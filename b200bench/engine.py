@@ -250,8 +250,6 @@ class NativeEngine:
         self.m_small = torch.zeros_like(self.master_small)
         self.v_small = torch.zeros_like(self.master_small)
         wte, wpe = Lt["transformer.wte.weight"], Lt["transformer.wpe.weight"]
-        self.stage_wte = torch.empty(wte.numel, dtype=BF16, device=dev)
-        self.stage_wpe = torch.empty(wpe.numel, dtype=BF16, device=dev)
         # "stream" mode: whole-block staging slots, block l lives in slot l % n_slots.  Two slots = gather again
         # in backward (full re-sharding after forward).  L slots = every block stays resident until the end of the
         # micro-step: ZeRO-3 when the model fits stage3_max_live_parameters (zero3.json:11, DeepSpeed keeps such
@@ -282,7 +280,22 @@ class NativeEngine:
         self.gather_ctas = (int(os.environ.get("B200BENCH_GATHER_CTAS", "0"))
                             or int(getattr(self.cfg, "gather_ctas", 0) or 0)
                             or min(128, max(32, (a1 - a0) * 2 // (2 << 20))))
-        self.stage_layer = (torch.empty(self.n_slots, a1 - a0, dtype=BF16, device=dev)
+        # Gather kernel.  From 4 ranks on: K16, ONE collective per range - every rank fetches 1/N of it from the
+        # owner and writes it into every rank's staging copy through the switch (a block lies inside one or two
+        # partitions: with every rank pulling the whole block, N-1 readers share one owner's links).  At 2 ranks
+        # there is one reader per owner either way: plain peer pull, no barriers.  B200BENCH_GATHER_COLL=1/0 forces.
+        gc = os.environ.get("B200BENCH_GATHER_COLL", "")
+        self.gather_coll = (self.ctx.world_size >= 4) if gc == "" else (gc != "0")
+        n_tab = wte.numel + wpe.numel
+        n_stage = n_tab + (self.n_slots * (a1 - a0) if self.param_gather == "stream" else 0)
+        if self.gather_coll:                  # K16 writes into the peers' staging buffers: symmetric allocation
+            self.stage_pb = self.comm.alloc("stage", n_stage, BF16)
+            self._stage = self.stage_pb.tensor
+        else:
+            self.stage_pb, self._stage = None, torch.empty(n_stage, dtype=BF16, device=dev)
+        self.stage_wte, self.stage_wpe = self._stage[:wte.numel], self._stage[wte.numel:n_tab]
+        self._stage_off = {"transformer.wte.weight": 0, "transformer.wpe.weight": wte.numel, "slots": n_tab}
+        self.stage_layer = (self._stage[n_tab:].view(self.n_slots, a1 - a0)
                             if self.param_gather == "stream" else None)
         self._invalidate_staging()
         # _slot_layer: block resident (or in flight) in each slot during this micro-step; _slot_done: comm-stream
@@ -322,10 +335,18 @@ class NativeEngine:
         ev.record(torch.cuda.current_stream())
         self.comm.stream.wait_event(ev)
         with torch.cuda.stream(self.comm.stream):
-            self.comm.gather_range(self.adj_table, self.stage_layer[slot], a, b - a, self.S, ctas=self.gather_ctas)
+            self._gather(self._stage_off["slots"] + slot * (b - a), a, b - a, self.gather_ctas)
         done = torch.cuda.Event()
         done.record(self.comm.stream)
         self._slot_layer[slot], self._slot_done[slot], self._slot_pending[slot] = l, done, True
+
+    def _gather(self, stage_off: int, flat_off: int, n: int, ctas: int = 0) -> None:
+        """Flat range [flat_off, flat_off + n) of the partitioned weights -> staging[stage_off:], current stream."""
+        if self.gather_coll:
+            self.comm.gather_bcast(self.adj_table, self.stage_pb, stage_off, flat_off, n, self.S)
+        else:
+            self.comm.gather_range(self.adj_table, self._stage[stage_off:stage_off + n], flat_off, n, self.S,
+                                   ctas=ctas or 128)
 
     def _layer_begin(self, l: int, step: int) -> None:
         """Stream-mode prefetch schedule: make block l resident for the compute stream, then start the gather of
@@ -356,9 +377,9 @@ class NativeEngine:
         o, P, p = self.ops, self.P, self.dropout
         B, T, d, H, hd = self.B, self.T, self.d, self.H, self.hd
         if self.sharded_params and self._regather_tables:   # embedding tables: plain peer gather up front
-            for name, stage in (("transformer.wte.weight", self.stage_wte), ("transformer.wpe.weight", self.stage_wpe)):
+            for name in ("transformer.wte.weight", "transformer.wpe.weight"):
                 s = self.layout[name]
-                self.comm.gather_range(self.adj_table, stage, s.offset, s.numel, self.S)
+                self._gather(self._stage_off[name], s.offset, s.numel)
         o.embedding_fwd(self.tokens, P["transformer.wte.weight"], P["transformer.wpe.weight"], self.x[0],
                         B, T, d, p, self._seed(-1, 0))
         for l in range(self.L):
@@ -770,5 +791,6 @@ class NativeEngine:
         if self.comm is not None:
             self.P, self.G = {}, {}
             self.grads = self.params = None
+            self._stage = self.stage_wte = self.stage_wpe = self.stage_layer = self.stage_pb = None
             self.comm.close()
             self.comm = None

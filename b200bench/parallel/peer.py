@@ -67,6 +67,8 @@ class PeerComm:
         L.b200_comm_gather_range.argtypes = [vp, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong, ctypes.c_ulonglong, i, vp]
         L.b200_comm_gather_range_from.argtypes = [vp, i, i, vp, ctypes.c_ulonglong, ctypes.c_ulonglong,
                                                   ctypes.c_ulonglong, i, vp]
+        ull = ctypes.c_ulonglong
+        L.b200_comm_gather_bcast.argtypes = [vp, vp, vp, vp, i, i, ull, ull, ull, ull, i, vp]
         L.b200_comm_allreduce_nvls.argtypes = [vp, vp, i, i, sz, sz, f, i, vp]
         L.b200_comm_rs_adamw_nvls.argtypes = [vp, vp, vp, vp, i, i, sz, sz, vp, vp, vp, vp, vp, i, vp, vp, i, vp]
         L.b200_peer_copy.argtypes = [vp, vp, sz, i, vp]
@@ -216,6 +218,20 @@ class PeerComm:
         if rc:
             raise _ops.NativeError(f"comm_gather_range failed with code {rc}")
         self.ops.launches += 1
+
+    def gather_bcast(self, table, dst: PeerBuffer, dst_off: int, flat_off: int, n: int, shard_elems: int,
+                     ctas: int = 0) -> None:
+        """K16: all-gather of the flat range into element offset dst_off of EVERY rank's copy of ``dst`` - a
+        collective (two rank barriers): every rank must call it with the same arguments in the same order.  Through
+        the NVSwitch multicast address of ``dst`` when it has one (B200BENCH_GATHER_MC=0: peer stores)."""
+        mc = dst.mc_ptr if os.environ.get("B200BENCH_GATHER_MC", "1") != "0" else 0
+        rc = self.ops.lib.b200_comm_gather_bcast(table, dst.table, c_void_p(mc) if mc else None, self.flags.table,
+                                                 self.rank, self.ws, flat_off, dst_off, n, shard_elems,
+                                                 ctas or (16 if mc else 32),
+                                                 c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc:
+            raise _ops.NativeError(f"comm_gather_bcast failed with code {rc}")
+        self.ops.launches += 2
 
     def peer_copy(self, src_ptr: int, dst: torch.Tensor, nbytes: int, ctas: int = 64) -> None:
         rc = self.ops.lib.b200_peer_copy(c_void_p(src_ptr), c_void_p(dst.data_ptr()), nbytes, ctas,

@@ -540,6 +540,63 @@ gather_range_kernel(PeerPtrs src, __nv_bfloat16* __restrict__ dst, unsigned long
   }
 }
 
+// ----------------------------------------------------------------------------------------
+// K16: all-gather of a flat range as ONE collective: rank r reads piece r of the range (1/WS of it) from the owning
+// partition(s) and writes it into EVERY rank's copy of the destination - through the NVSwitch multicast address
+// (one multimem.st, the switch replicates) when the destination has one, else by WS plain peer stores.
+// Why not let every rank pull the whole range (gather_range_kernel): a transformer block lies inside one or two
+// partitions, so WS-1 readers share ONE owner's NVLink egress (8 GPUs, 25 MB block: 240 us = 105 GB/s per reader,
+// measured).  Here the owner sends the range once in total and every rank receives it at its full ingress rate.
+// Cost: two rank barriers (all destination slots are free / all pieces have landed), flag plane 2.
+// rank < 0: test mode, blockIdx.y is the rank (one cooperative launch plays all ranks on one GPU).
+// ----------------------------------------------------------------------------------------
+template <int WS, bool MC>
+__global__ void __launch_bounds__(COMM_THREADS, MC ? 4 : 2)
+gather_bcast_kernel(PeerPtrs src, PeerPtrs dst, __nv_bfloat16* dst_mc, PeerPtrs flags, int rank_arg,
+                    unsigned long long flat_off, unsigned long long dst_off, unsigned long long n,
+                    unsigned long long shard) {
+  const int rank = rank_arg < 0 ? static_cast<int>(blockIdx.y) : rank_arg;
+  uint32_t* local = static_cast<uint32_t*>(flags.p[rank]);
+  const uint32_t epoch = local[EPOCH_OFF + 2];
+  rank_barrier(flags, rank, WS, 2, 2 * epoch + 1);  // every rank has stopped reading the destination's old content
+  constexpr int U = 8;
+  const size_t nvec = n >> 3;
+  const size_t per = (nvec + WS - 1) / WS;
+  const size_t v0 = per * rank;
+  const size_t v1 = (v0 + per < nvec) ? v0 + per : nvec;
+  const uint32_t vec0 = static_cast<uint32_t>(flat_off >> 3);
+  const uint32_t shard_vec = static_cast<uint32_t>(shard >> 3);
+  const size_t tstride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i0 = v0 + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i0 < v1; i0 += tstride * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * tstride;
+      if (i < v1) {
+        const uint32_t fv = vec0 + static_cast<uint32_t>(i);
+        const int owner = static_cast<int>(fv / shard_vec);
+        v[u] = ld_peer_v4(static_cast<const __nv_bfloat16*>(src.p[owner]) + static_cast<size_t>(fv) * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * tstride;
+      if (i < v1) {
+        if constexpr (MC) {
+          multimem_st_bf16x8(dst_mc + dst_off + i * 8, v[u]);
+        } else {
+#pragma unroll
+          for (int r = 0; r < WS; ++r) {
+            const int q = (rank + r) % WS;   // own copy first, then the peers in a rank-specific order
+            st_peer_v4(static_cast<__nv_bfloat16*>(dst.p[q]) + dst_off + i * 8, v[u]);
+          }
+        }
+      }
+    }
+  }
+  rank_barrier(flags, rank, WS, 2, 2 * epoch + 2);  // every rank's pieces have landed here
+}
+
 static PeerPtrs make_ptrs(void* const* arr, int ws) {
   PeerPtrs p;
   for (int i = 0; i < MAX_RANKS; ++i) p.p[i] = i < ws ? arr[i] : nullptr;
@@ -761,6 +818,61 @@ extern "C" int b200_comm_gather_range_from(void* const* shard_adj, int ws, int r
   gather_range_kernel<<<ctas > 0 ? ctas : 128, COMM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       make_ptrs(shard_adj, ws), static_cast<__nv_bfloat16*>(dst), flat_off, n, shard_elems,
       ws > 0 ? (n >> 3) * static_cast<unsigned long long>(rank < 0 ? 0 : rank % ws) / ws : 0ull);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- K16 -------------------------------------------------------------------------------------
+// dst_tab[r] = rank r's copy of the destination buffer, dst_mc = this rank's multicast address of it (or null:
+// plain peer stores); the range lands at element offset dst_off of every copy.
+static int gather_bcast_check(int ws, unsigned long long flat_off, unsigned long long dst_off, unsigned long long n,
+                              unsigned long long shard_elems) {
+  if (n % 8 || flat_off % 8 || dst_off % 8 || shard_elems % 8 || ws > MAX_RANKS) return -2;
+  if (((flat_off + n) >> 3) > 0xFFFFFFFFull || (shard_elems >> 3) > 0xFFFFFFFFull || shard_elems == 0) return -3;
+  return 0;
+}
+
+extern "C" int b200_comm_gather_bcast(void* const* shard_adj, void* const* dst_tab, void* dst_mc,
+                                      void* const* flags, int rank, int ws, unsigned long long flat_off,
+                                      unsigned long long dst_off, unsigned long long n,
+                                      unsigned long long shard_elems, int ctas, void* stream) {
+  if (int rc = gather_bcast_check(ws, flat_off, dst_off, n, shard_elems)) return rc;
+  if (rank < 0 || rank >= ws) return -2;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  PeerPtrs src = make_ptrs(shard_adj, ws), dst = make_ptrs(dst_tab, ws), f = make_ptrs(flags, ws);
+  DISPATCH_WS(ws, {
+    if (dst_mc != nullptr) {
+      ctas = clamp_ctas(ctas, 32, resident_cta_limit(gather_bcast_kernel<W, true>, COMM_THREADS));
+      gather_bcast_kernel<W, true><<<ctas, COMM_THREADS, 0, s>>>(src, dst, static_cast<__nv_bfloat16*>(dst_mc), f,
+                                                                 rank, flat_off, dst_off, n, shard_elems);
+    } else {
+      ctas = clamp_ctas(ctas, 32, resident_cta_limit(gather_bcast_kernel<W, false>, COMM_THREADS));
+      gather_bcast_kernel<W, false><<<ctas, COMM_THREADS, 0, s>>>(src, dst, nullptr, f, rank, flat_off, dst_off, n,
+                                                                  shard_elems);
+    }
+  });
+  comm_bump_epoch_kernel<<<1, 1, 0, s>>>(static_cast<uint32_t*>(flags[rank]), 2);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// Test mode of K16 (peer-store path): one cooperative launch plays all ws ranks on the current GPU.
+extern "C" int b200_comm_gather_bcast_loop(void* const* shard_adj, void* const* dst_tab, void* const* flags, int ws,
+                                           unsigned long long flat_off, unsigned long long dst_off,
+                                           unsigned long long n, unsigned long long shard_elems, int ctas,
+                                           void* stream) {
+  if (int rc = gather_bcast_check(ws, flat_off, dst_off, n, shard_elems)) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  PeerPtrs src = make_ptrs(shard_adj, ws), dst = make_ptrs(dst_tab, ws), f = make_ptrs(flags, ws);
+  __nv_bfloat16* mc = nullptr;
+  int rank = -1;
+  void* args[] = {&src, &dst, &mc, &f, &rank, &flat_off, &dst_off, &n, &shard_elems};
+  DISPATCH_WS(ws, {
+    ctas = clamp_ctas(ctas, 8, resident_cta_limit(gather_bcast_kernel<W, false>, COMM_THREADS) / ws);
+    if (ctas < 1) return -9;
+    cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(gather_bcast_kernel<W, false>), dim3(ctas, ws),
+                                                dim3(COMM_THREADS), args, 0, s);
+    if (e != cudaSuccess) return static_cast<int>(e);
+  });
+  comm_bump_epoch_all_kernel<<<1, 1, 0, s>>>(f, ws, 2);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -227,6 +227,17 @@ int b200_comm_gather_range_from(void* const* shard_adj, int ws, int rank, void* 
 int b200_comm_gather_range(void* const* shard_adj, int ws, void* dst, unsigned long long flat_off,
                            unsigned long long n, unsigned long long shard_elems, int ctas,
                            void* stream);
+/* K16: the same gather as ONE collective.  Rank r reads piece r (1/ws) of the range from its owner(s) and writes it
+ * at element offset dst_off into every rank's copy of the destination: one multimem.st through dst_mc (this rank's
+ * NVSwitch multicast address of the destination buffer) or, with dst_mc == NULL, ws peer stores through dst_tab.
+ * The owner sends the range once in total instead of once per reader.  Two rank barriers on flag plane 2: every
+ * rank must issue the same sequence of K16 calls.  _loop: test mode, one cooperative launch plays all ranks. */
+int b200_comm_gather_bcast(void* const* shard_adj, void* const* dst_tab, void* dst_mc, void* const* flags, int rank,
+                           int ws, unsigned long long flat_off, unsigned long long dst_off, unsigned long long n,
+                           unsigned long long shard_elems, int ctas, void* stream);
+int b200_comm_gather_bcast_loop(void* const* shard_adj, void* const* dst_tab, void* const* flags, int ws,
+                                unsigned long long flat_off, unsigned long long dst_off, unsigned long long n,
+                                unsigned long long shard_elems, int ctas, void* stream);
 /* dst[i] = src[i] with 16-byte volatile loads: P2P bandwidth probe when src is peer memory. */
 int b200_peer_copy(const void* src, void* dst, size_t bytes, int ctas, void* stream);
 

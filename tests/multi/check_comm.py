@@ -124,6 +124,29 @@ def main():
             extra += f" norm={gn[0].item():.3f} ref={math.sqrt(ss.item()):.3f}"
         report(f"K15 rs_adamw clip={clip}", e_master < 2e-3 and e_push < 2e-2, extra)
 
+    # ---- K16 all-gather as one collective: both data paths, two launches each (epoch advance) ---------------------
+    shard = n // ws // 8 * 8
+    torch.manual_seed(11)
+    wfull = torch.randn(shard * ws, device=dev).to(torch.bfloat16)          # same on every rank
+    ws_pb = comm.alloc("k16_shard", shard, torch.bfloat16)
+    ws_pb.tensor.copy_(wfull[rank * shard:(rank + 1) * shard])
+    st_pb = comm.alloc("k16_stage", shard * ws + 256, torch.bfloat16)
+    tab = comm.adjusted_table(ws_pb, shard)
+    torch.cuda.synchronize(dev); dist.barrier()
+    for mc in ((1, 0) if st_pb.mc_ptr else (0,)):
+        os.environ["B200BENCH_GATHER_MC"] = str(mc)
+        okk = True
+        for g_off, g_n, d_off in ((0, shard * ws, 128), (shard - 8 * 40, 8 * 1000, 8)):
+            st_pb.tensor.fill_(-1.0)
+            torch.cuda.synchronize(dev); dist.barrier()
+            comm.gather_bcast(tab, st_pb, d_off, g_off, g_n, shard)
+            torch.cuda.synchronize(dev); dist.barrier()
+            t = st_pb.tensor
+            okk = okk and torch.equal(t[d_off:d_off + g_n], wfull[g_off:g_off + g_n]) \
+                and bool((t[:d_off] == -1).all()) and bool((t[d_off + g_n:] == -1).all())
+        report(f"K16 gather_bcast ({'multicast' if mc else 'peer stores'})", okk)
+    os.environ.pop("B200BENCH_GATHER_MC", None)
+
     # ---- engine: fused vs NCCL schedule, same data, dropout 0 ----------------------------------------
     from b200bench.config import StrategyConfig, get_model_config, load_deepspeed_config
     from b200bench.engine import NativeEngine
@@ -131,9 +154,18 @@ def main():
     # fsdp / zero3 are checked with both weight all-gather schedules (inside the GEMM, and per block on the
     # comm stream); each fused run is compared with the NCCL schedule of the same strategy
     # the last case accumulates over 2 micro-steps: the second one reuses the blocks gathered by the first
-    for strat, pg, accum in (("ddp", None, 1), ("zero2", None, 1), ("fsdp", "stream", 1), ("fsdp", "gemm", 1),
-                             ("zero3", "stream", 1), ("zero3", "gemm", 1), ("zero3", "stream", 2)):
+    # "stream+pull" / "stream+k16": the block gathers as plain peer pulls or as the K16 collective (both forced, whatever
+    # the default for this world size is)
+    for strat, pg, accum in (("ddp", None, 1), ("zero2", None, 1), ("fsdp", "stream+pull", 1), ("fsdp", "stream+k16", 1),
+                             ("fsdp", "gemm", 1), ("zero3", "stream+pull", 1), ("zero3", "stream+k16", 1),
+                             ("zero3", "gemm", 1), ("zero3", "stream+k16", 2)):
         cfgm = get_model_config("T", 128)
+        label = pg
+        if pg and "+" in pg:
+            os.environ["B200BENCH_GATHER_COLL"] = "1" if pg.endswith("k16") else "0"
+            pg = "stream"
+        else:
+            os.environ.pop("B200BENCH_GATHER_COLL", None)
         sds = []
         for mode in ("fused", "nccl"):
             if strat in ("zero2", "zero3"):
@@ -154,8 +186,10 @@ def main():
         # replicas must agree across ranks as well
         w = sds[0][0]["transformer.h.0.mlp.0.weight"].clone()
         w2 = w.clone(); dist.broadcast(w2, 0)
-        report(f"engine {strat}{'/' + pg if pg else ''}{' accum ' + str(accum) if accum > 1 else ''}: fused == nccl", worst < 5e-3 and torch.equal(w, w2),
+        report(f"engine {strat}{'/' + label if label else ''}{' accum ' + str(accum) if accum > 1 else ''}: fused == nccl", worst < 5e-3 and torch.equal(w, w2),
                f"max_param_diff={worst:.2e} loss={sds[0][1]:.4f}/{sds[1][1]:.4f}")
+
+    os.environ.pop("B200BENCH_GATHER_COLL", None)
 
     # ---- bandwidth / latency probes -----------------------------------------------------------------
     if a.bench:
@@ -212,6 +246,16 @@ def main():
                 if rank == 0:
                     print(f"[bench] gather_range {cnt*2/1e6:6.1f} MB ctas={ctas:3d}: {ms*1e3:7.1f} us  "
                           f"{cnt*2/ms/1e6:5.0f} GB/s", flush=True)
+            # K16: the same range as one collective (1/ws fetched per rank, written to every rank through the switch
+            # or by peer stores) into a symmetric destination
+            for mc in ((1, 0) if gk.mc_ptr else (0,)):
+                os.environ["B200BENCH_GATHER_MC"] = str(mc)
+                for ctas in (8, 16, 32, 64):
+                    ms = timed(lambda: comm.gather_bcast(table, gk, 0, 0, cnt, shard, ctas=ctas), 10, ws, dev)
+                    if rank == 0:
+                        print(f"[bench] K16 gather_bcast {cnt*2/1e6:6.1f} MB {'multicast' if mc else 'peer st  '} "
+                              f"ctas={ctas:3d}: {ms*1e3:7.1f} us  {cnt*2/ms/1e6:5.0f} GB/s", flush=True)
+            os.environ.pop("B200BENCH_GATHER_MC", None)
     comm.close()
     dist.barrier()
     if rank == 0:

@@ -148,3 +148,27 @@ def test_gather_range_single_process(native):
             rc = L.b200_comm_gather_range_from(adj, ws, rank, c_void_p(dst.data_ptr()), off, n2, shard, 3, _stream())
             assert rc == 0
             assert torch.equal(dst, full[off:off + n2]), (rank, n2)
+
+
+@pytest.mark.parametrize("ws", [2, 4, 8])
+def test_gather_bcast_loopback(native, ws):
+    """K16 (peer-store path): every rank fetches 1/ws of the range from its owner(s) and writes it into every rank's
+    destination copy; back-to-back epochs reuse flag plane 2; bytes outside the destination range stay untouched."""
+    L = _lib(native)
+    ull = ctypes.c_ulonglong
+    L.b200_comm_gather_bcast_loop.argtypes = [c_void_p, c_void_p, c_void_p, c_int, ull, ull, ull, ull, c_int, c_void_p]
+    torch.manual_seed(70 + ws)
+    shard = 8 * 640
+    flags = [torch.zeros(int(L.b200_comm_flag_bytes()), dtype=torch.uint8, device=DEV) for _ in range(ws)]
+    for epoch, (off, n, dst_off, ctas) in enumerate([(8 * 100, 8 * 1100, 8 * 16, 4), (0, 8 * 3, 0, 2),
+                                                     (8 * 630, 8 * 601, 8 * 64, 8), (8 * 5, shard * ws - 8 * 5, 0, 3)]):
+        full = torch.randn(ws * shard, device=DEV).to(BF16)
+        shards = [full[r * shard:(r + 1) * shard].clone() for r in range(ws)]
+        adj = (c_void_p * ws)(*[shards[r].data_ptr() - r * shard * 2 for r in range(ws)])
+        dsts = [torch.full((dst_off + n + 64,), float(r + 1), dtype=BF16, device=DEV) for r in range(ws)]
+        rc = L.b200_comm_gather_bcast_loop(adj, _table(dsts), _table(flags), ws, off, dst_off, n, shard, ctas, _stream())
+        assert rc == 0, rc
+        torch.cuda.synchronize()
+        for r in range(ws):
+            assert torch.equal(dsts[r][dst_off:dst_off + n], full[off:off + n]), (epoch, r)
+            assert bool((dsts[r][:dst_off] == r + 1).all()) and bool((dsts[r][dst_off + n:] == r + 1).all()), (epoch, r)

@@ -39,16 +39,24 @@ def test_ddp_gloo_ws2_plumbing(tmp_path):
 def test_ddp_equals_fsdp_and_uniform_zero(tmp_path):
     """Same data, dropout 0: after k steps DDP == FSDP == ZeRO-2 == ZeRO-3 parameters.
     The ZeRO configs add clipping + WarmupLR, so they are compared with each other."""
+    def same(a, b, k):
+        if k.endswith("in_proj_bias"):
+            # the key bias has no true gradient (softmax is invariant to it): what reaches Adam is summation-order
+            # noise, which Adam normalises to +-lr per step - compare the query and value parts only
+            d = a.numel() // 3
+            return torch.allclose(a[:d], b[:d], atol=1e-6) and torch.allclose(a[2 * d:], b[2 * d:], atol=1e-6)
+        return torch.allclose(a, b, atol=1e-6)
+
     _, ddp = _run(tmp_path, "ddp", 2)
     _, fsdp = _run(tmp_path, "fsdp", 2)
     for k in ddp:
-        assert torch.allclose(ddp[k], fsdp[k], atol=1e-6), k
+        assert same(ddp[k], fsdp[k], k), k
     _, z2 = _run(tmp_path, "zero2", 2, extra=["--grad-accum-mode", "uniform"])
     z3cfg = ["--deepspeed-config", os.path.join(ROOT, "configs/deepspeed/zero3.json"),
              "--grad-accum-mode", "uniform"]
     _, z3 = _run(tmp_path, "zero3", 2, extra=z3cfg)
     for k in z2:
-        assert torch.allclose(z2[k], z3[k], atol=1e-6), k
+        assert same(z2[k], z3[k], k), k
 
 
 def test_rank_failure_propagates(tmp_path):
