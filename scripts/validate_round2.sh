@@ -6,7 +6,7 @@ mkdir -p gpurun_out/n$N
 P=$((29500 + RANDOM % 300))
 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $P tests/multi/check_comm.py --bench > gpurun_out/n$N/check_comm.log 2>&1; echo "check_comm rc=$?"
 grep -E "^\[check\]" gpurun_out/n$N/check_comm.log | tail -20
-grep -E "^\[bench\] allreduce +(25|256) MiB|K15|gather_range" gpurun_out/n$N/check_comm.log
+grep -E "^\[bench\] allreduce +(25|256) MiB|K15|gather_range|K16" gpurun_out/n$N/check_comm.log
 P=$((P + 1))
 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $P bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/n$N/bench.json 2> gpurun_out/n$N/bench.err; echo "bench rc=$?"
 python - <<PY
