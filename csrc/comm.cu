@@ -14,6 +14,8 @@
 //                            own shard (ZeRO-3 / FSDP)
 //   K13-NVLS                 the same all-reduce through an NVSwitch multicast mapping: multimem.ld_reduce sums
 //                            the ranks' copies inside the switch, multimem.st writes the result to every rank
+//   K16  gather_bcast        all-gather of a weight range (FSDP / ZeRO-3 block gathers): each rank fetches 1/N of the
+//                            range from its owner and multimem.st writes it into every rank's staging buffer
 // Every kernel can also run as ONE cooperative launch that plays all ranks (gridDim.y = ranks, rank = blockIdx.y)
 // over per-"rank" buffers on a single GPU: that is how the protocols are tested where only one GPU exists.
 // Every NVSwitch peer is one hop away at full bandwidth, so direct one-/two-shot algorithms are used;
