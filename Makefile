@@ -19,9 +19,9 @@ $(LIB): $(OBJS)
 	@mkdir -p b200bench/lib
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
 
-build/bin/%: csrc/tests/%.cu $(OBJS) $(wildcard csrc/tests/*.cu)
+build/bin/%: csrc/tests/%.cu $(OBJS) $(wildcard csrc/tests/*.cu csrc/tests/*.h)
 	@mkdir -p build/bin
-	$(NVCC) $(NVCCFLAGS) $< $(OBJS) -o $@
+	$(NVCC) $(NVCCFLAGS) $< $(OBJS) -o $@ -ldl -lpthread
 
 ptxas-info:
 	@for f in $(SRCS); do echo "== $$f"; $(NVCC) $(NVCCFLAGS) -Xptxas -v -c $$f -o /dev/null 2>&1 | grep -E "registers|spill" ; done

@@ -1,4 +1,5 @@
 // Standalone numerics + timing harness for the fused attention kernels (forward and backward).
+#include "clock_sampler.h"
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
@@ -213,6 +214,8 @@ int main(int argc, char** argv) {
   printf("== attention numerics: %d failing case(s) ==\n", fails);
   if (small) return fails ? 1 : 0;
   printf("== attention timing ==\n");
+  clocks::Sampler sampler;
+  sampler.start();
   time_case(1, 2048, 16, 0, false, 0.f);
   time_case(1, 2048, 16, 0, false, 0.1f);
   time_case(1, 2048, 16, 1, false, 0.f);
@@ -223,5 +226,6 @@ int main(int argc, char** argv) {
     time_case(1, 2048, 16, 0, true, 0.1f);
     time_case(8, 2048, 16, 0, true, 0.f);
   }
+  sampler.stop_and_print("attention timing section");
   return fails ? 1 : 0;
 }

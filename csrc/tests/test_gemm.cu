@@ -1,5 +1,6 @@
 // Standalone numerics + timing harness for b200_gemm_bf16 (no torch needed, starts in < 1 s).
 // Usage: test_gemm [--time | small]   (small: numerics on the small shapes only, for compute-sanitizer)
+#include "clock_sampler.h"
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
@@ -341,6 +342,8 @@ int main(int argc, char** argv) {
   printf("== gemm numerics: %d failing case(s) ==\n", fails);
   if (argc > 1 && !small) {
     printf("== gemm timing ==\n");
+    clocks::Sampler sampler;
+    sampler.start();
     time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 0, "qkv fwd (auto)");
     time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 2128, "qkv fwd pair");
     time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 2256, "qkv fwd pair");
@@ -365,6 +368,8 @@ int main(int argc, char** argv) {
     time_case(2048, 32000, 1024, 0, 0, B200_EPI_NONE, 256, "lm_head fwd");
     time_case(8192, 8192, 8192, 0, 0, B200_EPI_NONE, 128, "square 8k");
     time_case(8192, 8192, 8192, 0, 0, B200_EPI_NONE, 256, "square 8k");
+    sampler.stop_and_print("gemm timing, plain shapes");
+    sampler.start();
     printf("== multicast / bias-gradient variants ==\n");
     for (int u : {1, 2, 4, 8}) time_case(2048, 3072, 1024, 0, 0, B200_EPI_BIAS, 2256, "qkv fwd pair mc", u);
     for (int u : {1, 2, 4, 8}) time_case(2048, 1024, 4096, 0, 1, B200_EPI_NONE, 2256, "fc1 dgrad pair mc", u);
@@ -374,6 +379,7 @@ int main(int argc, char** argv) {
     time_case(4096, 1024, 2048, 1, 1, B200_EPI_NONE, 0, "fc1 wgrad", 0, 0);
     time_case(4096, 1024, 2048, 1, 1, B200_EPI_NONE, 0, "fc1 wgrad + dbias", 0, 1);
     time_case(1024, 1024, 2048, 1, 1, B200_EPI_NONE, 0, "proj wgrad + dbias", 0, 1);
+    sampler.stop_and_print("gemm timing section");
   }
   return fails ? 1 : 0;
 }

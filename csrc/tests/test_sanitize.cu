@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "../../include/b200bench.h"
+#include "clock_sampler.h"   // before the namespaces below: the harness sources include it too
 
 namespace gemm_t {
 #define main harness_main

@@ -193,6 +193,8 @@ def main():
 
     # ---- bandwidth / latency probes -----------------------------------------------------------------
     if a.bench:
+        from b200bench.utils.clocks import ClockSampler
+        sampler = ClockSampler(lr).start()            # SM clocks / throttle reasons while the probes below run
         nbytes = 256 * 1024 * 1024
         big = comm.alloc("big", nbytes // 2, torch.bfloat16)
         dst = torch.empty(nbytes // 2, dtype=torch.bfloat16, device=dev)
@@ -256,6 +258,11 @@ def main():
                         print(f"[bench] K16 gather_bcast {cnt*2/1e6:6.1f} MB {'multicast' if mc else 'peer st  '} "
                               f"ctas={ctas:3d}: {ms*1e3:7.1f} us  {cnt*2/ms/1e6:5.0f} GB/s", flush=True)
             os.environ.pop("B200BENCH_GATHER_MC", None)
+        ck = sampler.stop()
+        allck = [None] * ws
+        dist.all_gather_object(allck, {k: ck.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons")})
+        if rank == 0:
+            print(f"[clocks] bandwidth probes, per rank: {allck}", flush=True)
     comm.close()
     dist.barrier()
     if rank == 0:
