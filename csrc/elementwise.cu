@@ -499,48 +499,96 @@ embedding_fwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restric
   }
 }
 
-// Backward: dwte[tok[m],:] += mask(dx[m,:]) (atomic: tokens repeat), dwpe[t,:] += sum_b mask(dx[b,t,:]).
-__global__ void __launch_bounds__(256)
+// Backward: dwte[tok[m],:] += sum over the positions holding that token of mask(dx[m,:]), dwpe[t,:] (+)= sum_b
+// mask(dx[b,t,:]).  Tokens repeat (heavily at a 512-word vocabulary, and in real text), and dwte already holds the
+// lm_head weight gradient of the tied matrix: adding position by position in bf16 would round after every add and
+// depend on the order of the atomics.  Instead ONE CTA owns each distinct token - the CTA of the token's first
+// position: it collects the later positions with the same token in increasing order (ballot compaction, 4096
+// positions per round), sums their rows in fp32 and adds the sum to the dwte row once, without atomics.  The result
+// is deterministic and rounded once per 4096 positions.  CTAs of repeated positions exit after the scan.
+// One CTA per position m; the CTAs of batch element 0 also own the position-embedding row t = m.
+constexpr int EB_THREADS = 128;
+constexpr int EB_SEG = 4096;                       // positions per compaction round
+constexpr int EB_WARPS = EB_THREADS / 32;
+constexpr int EB_PER_WARP = EB_SEG / EB_WARPS;
+
+__global__ void __launch_bounds__(EB_THREADS)
 embedding_bwd_kernel(const int* __restrict__ tok, const __nv_bfloat16* __restrict__ dx,
                      __nv_bfloat16* __restrict__ dwte, __nv_bfloat16* __restrict__ dwpe, int B, int T,
                      int d, uint32_t thr, float scale, uint32_t seed, int accumulate_wpe,
                      const uint32_t* __restrict__ seed_ptr) {
   pdl_wait();
   if (thr && seed_ptr) seed ^= __ldg(seed_ptr);
-  const int nvec = d >> 3;
-  const size_t total = static_cast<size_t>(T) * nvec;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int t = static_cast<int>(i / nvec), c = static_cast<int>(i % nvec);
-    float pos[8];
+  __shared__ int s_list[EB_WARPS][EB_PER_WARP];
+  __shared__ int s_n[EB_WARPS];
+  const int M = B * T, m = blockIdx.x, nvec = d >> 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  auto load_masked = [&](int row, int c, float (&g)[8]) {
+    unpack8(reinterpret_cast<const uint4*>(dx + static_cast<size_t>(row) * d)[c], g);
+    if (thr) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) pos[j] = 0.f;
-    for (int b = 0; b < B; ++b) {
-      const int m = b * T + t;
-      float g[8];
-      unpack8(reinterpret_cast<const uint4*>(dx + static_cast<size_t>(m) * d)[c], g);
-      if (thr) {
+      for (int j = 0; j < 8; ++j) {
+        const uint64_t idx = static_cast<uint64_t>(row) * d + c * 8 + j;
+        g[j] = dropout_keep(seed, idx, thr) ? g[j] * scale : 0.f;
+      }
+    }
+  };
+  // ---- position embedding: row t = m, summed over the batch ---------------------------------
+  if (m < T) {
+    for (int c = threadIdx.x; c < nvec; c += EB_THREADS) {
+      float pos[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int b = 0; b < B; ++b) {
+        float g[8];
+        load_masked(b * T + m, c, g);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint64_t idx = static_cast<uint64_t>(m) * d + c * 8 + j;
-          g[j] = dropout_keep(seed, idx, thr) ? g[j] * scale : 0.f;
+        for (int j = 0; j < 8; ++j) pos[j] += g[j];
+      }
+      uint4* pw = reinterpret_cast<uint4*>(dwpe + static_cast<size_t>(m) * d) + c;
+      if (accumulate_wpe) {
+        float old[8];
+        unpack8(*pw, old);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) pos[j] += old[j];
+      }
+      *pw = pack8(pos);
+    }
+  }
+  // ---- token embedding: only the first position of a token goes on ---------------------------
+  const int id = tok[m];
+  int earlier = 0;
+  for (int j = threadIdx.x; j < m; j += EB_THREADS) earlier |= (tok[j] == id);
+  if (__syncthreads_or(earlier)) return;
+  for (int s0 = (m / EB_SEG) * EB_SEG; s0 < M; s0 += EB_SEG) {
+    int n = 0;                                  // warp-uniform: matches found by this warp so far
+    for (int k = 0; k < EB_PER_WARP; k += 32) {
+      const int j = s0 + warp * EB_PER_WARP + k + lane;
+      const bool hit = j >= m && j < M && tok[j] == id;
+      const unsigned mask = __ballot_sync(0xffffffffu, hit);
+      if (hit) s_list[warp][n + __popc(mask & ((1u << lane) - 1u))] = j;
+      n += __popc(mask);
+    }
+    if (lane == 0) s_n[warp] = n;
+    __syncthreads();
+    for (int c = threadIdx.x; c < nvec; c += EB_THREADS) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int w = 0; w < EB_WARPS; ++w) {
+        const int nw = s_n[w];
+#pragma unroll 4
+        for (int i = 0; i < nw; ++i) {
+          float g[8];
+          load_masked(s_list[w][i], c, g);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += g[j];
         }
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) pos[j] += g[j];
-      __nv_bfloat162* dst =
-          reinterpret_cast<__nv_bfloat162*>(dwte + static_cast<size_t>(tok[m]) * d + c * 8);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) atomicAdd(dst + j, __floats2bfloat162_rn(g[2 * j], g[2 * j + 1]));
-    }
-    uint4* pw = reinterpret_cast<uint4*>(dwpe + static_cast<size_t>(t) * d) + c;
-    if (accumulate_wpe) {
+      uint4* pw = reinterpret_cast<uint4*>(dwte + static_cast<size_t>(id) * d) + c;
       float old[8];
       unpack8(*pw, old);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) pos[j] += old[j];
+      for (int j = 0; j < 8; ++j) acc[j] += old[j];
+      *pw = pack8(acc);
     }
-    *pw = pack8(pos);
+    __syncthreads();                            // the lists are rebuilt in the next round
   }
 }
 
@@ -1001,9 +1049,8 @@ extern "C" int b200_embedding_bwd(const int* tokens, const void* dx, void* dwte,
                                   void* stream) {
   if (d % 8) return -2;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const size_t work = static_cast<size_t>(T) * (d / 8);
   const float scale = drop_p > 0.f && drop_p < 1.f ? 1.f / (1.f - drop_p) : 1.f;
-  launch_pdl(embedding_bwd_kernel, dim3(grid_for(work, 256, 8)), dim3(256), 0, s, 
+  launch_pdl(embedding_bwd_kernel, dim3(B * T), dim3(EB_THREADS), 0, s, 
       tokens, static_cast<const __nv_bfloat16*>(dx), static_cast<__nv_bfloat16*>(dwte),
       static_cast<__nv_bfloat16*>(dwpe), B, T, d, drop_thr(drop_p), scale, seed, accumulate_wpe,
       step_seed_ptr());

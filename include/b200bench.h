@@ -114,7 +114,8 @@ int b200_colsum_static(const void* dy, void* out, int M, int N, int ld, int accu
 /* ---- embedding (TH:85-89) ------------------------------------------------------ */
 int b200_embedding_fwd(const int* tokens, const void* wte, const void* wpe, void* out, int B,
                        int T, int d, float drop_p, unsigned int seed, void* stream);
-/* dwte[tok] += dx (atomic, lands on top of the tied lm_head wgrad), dwpe[t] (+)= sum_b dx */
+/* dwte[tok] += sum of dx over the positions holding tok: summed in fp32 by the one CTA that owns the token and added
+ * once to the row (on top of the tied lm_head wgrad) - no atomics, deterministic; dwpe[t] (+)= sum_b dx */
 int b200_embedding_bwd(const int* tokens, const void* dx, void* dwte, void* dwpe, int B, int T,
                        int d, float drop_p, unsigned int seed, int accumulate_wpe, void* stream);
 
