@@ -8,26 +8,29 @@ import re
 import subprocess
 import sys
 
-COLS = [("gpu__time_duration.sum", "us", 1e-3), ("launch__grid_size", "grid", 1), ("launch__block_size", "block", 1),
-        ("launch__registers_per_thread", "regs", 1),
-        ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "SM %", 1),
-        ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor %", 1),
-        ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue %", 1),
-        ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "DRAM %", 1),
-        ("lts__t_bytes.sum", "L2 MB", 1e-6)]
+COLS = [("gpu__time_duration.sum", "us", "time"), ("launch__grid_size", "grid", ""), ("launch__block_size", "block", ""),
+        ("launch__registers_per_thread", "regs", ""),
+        ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "SM %", ""),
+        ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor %", ""),
+        ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue %", ""),
+        ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "DRAM %", ""),
+        ("lts__t_bytes.sum", "L2 MB", "bytes")]
 STALLS = "smsp__pcsamp_warps_issue_stalled_"
+# ncu prints a value in whatever unit fits its magnitude
+TO_US = {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6}
+TO_MB = {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
 
 
-def num(v, unit, scale):
+def num(v, unit, kind):
     try:
         x = float(v.replace(",", ""))
     except ValueError:
         return v
-    # ncu prints durations in ns / us / ms and bytes in byte / Kbyte / Mbyte depending on magnitude
-    mult = {"nsecond": 1e-3 / 1e-3, "usecond": 1e3 * 1e-3 / 1e-3, "msecond": 1e6, "second": 1e9,
-            "byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
-    x = x * mult * scale
-    return f"{x:.1f}" if abs(x) < 1000 and x != int(x) else f"{x:.0f}"
+    if kind == "time":
+        x *= TO_US.get(unit, 1.0)
+    elif kind == "bytes":
+        x *= TO_MB.get(unit, 1e-6)
+    return f"{x:.0f}" if x == int(x) or abs(x) >= 1000 else f"{x:.1f}"
 
 
 def main():
