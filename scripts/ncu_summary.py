@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Summarise an .ncu-rep (captured with `ncu --set full --import-source on`) into markdown: headline
 metrics from the raw page, opcode mix and the hottest source lines from the source page.
-Usage: scripts/ncu_summary.py gpurun_out/prof_x.ncu-rep > profiles/x_ncu.md"""
+Usage: scripts/ncu_summary.py gpurun_out/prof_x.ncu-rep [launch index in the report, default 0] > profiles/x_ncu.md"""
 import collections
 import csv
 import io
@@ -18,8 +18,12 @@ WANT = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
 STALLS = "smsp__pcsamp_warps_issue_stalled_"
 
 
+SKIP = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+
+
 def page(rep, name):
-    out = subprocess.run(["ncu", "-i", rep, "--page", name, "--csv"], capture_output=True, text=True).stdout
+    out = subprocess.run(["ncu", "-i", rep, "--launch-skip", str(SKIP), "--launch-count", "1", "--page", name, "--csv"],
+                         capture_output=True, text=True).stdout
     return list(csv.reader(io.StringIO(out)))
 
 
@@ -28,7 +32,7 @@ def main():
     raw = page(rep, "raw")
     hdr, units, vals = raw[0], raw[1], raw[2]
     d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
-    print(f"# ncu summary: {rep.split('/')[-1]}\n")
+    print(f"# ncu summary: {rep.split('/')[-1]}" + (f", launch {SKIP}" if SKIP else "") + "\n")
     print(f"Kernel: `{d.get('Kernel Name', ('?',))[0]}`\n")
     print("| metric | value | unit |\n|---|---|---|")
     for k in WANT:
@@ -43,17 +47,21 @@ def main():
     ia, isamp, iex = h.index("Source"), h.index("# Samples"), h.index("Instructions Executed")
     ops = collections.Counter()
     samp = collections.Counter()
-    rows = src[2:]
+    rows = [r for r in src[2:] if len(r) > max(ia, isamp, iex)]
     for r in rows:
         m = re.match(r"\s*(@!?U?P\d+\s+)?([A-Z0-9_.]+)", r[ia])
         o = m.group(2).split(".")[0] if m else "?"
-        ops[o] += int(r[iex] or 0)
-        samp[o] += int(r[isamp] or 0)
+        try:
+            ops[o] += int(r[iex] or 0)
+            samp[o] += int(r[isamp] or 0)
+        except ValueError:        # a repeated header row (several source views in one page)
+            continue
     ti, ts = sum(ops.values()) or 1, sum(samp.values()) or 1
     print("\nOpcode mix (executed warp instructions / stall samples):\n")
     print("| opcode | inst % | samples % |\n|---|---|---|")
     for o, n in ops.most_common(14):
         print(f"| {o} | {100*n/ti:.1f} | {100*samp[o]/ts:.1f} |")
+    rows = [r for r in rows if (r[isamp] or "0").isdigit()]
     hot = sorted(rows, key=lambda r: -int(r[isamp] or 0))[:10]
     print("\nHottest SASS lines by samples:\n")
     for r in hot:
