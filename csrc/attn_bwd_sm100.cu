@@ -209,6 +209,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     const int tid = threadIdx.x - 128;   // 0..255
     const bool drop = p.drop_threshold != 0;
     const uint32_t thr32 = p.drop_threshold;   // p * 2^32
+    const float lg_rescale = drop ? log2f(p.drop_scale) : 0.f;   // drop_scale = 1/(1-p)
+    const float inv_rescale = drop ? 1.f / p.drop_scale : 1.f;
     const uint32_t colkey = drop_colkey(seed, static_cast<uint32_t>(bh) * p.T + krow);   // b(k) of this thread's key
     uint8_t* rowP = nullptr;   // set per query block: P/dS buffer (i & 1)
     uint8_t* rowS = nullptr;
@@ -254,10 +256,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
             float dp = __uint_as_float(vd[c][e]);
             float pd = pv;
             if (DROP) {
-              // dS = P * (keep ? dP/(1-p) : 0 - D);  the dropped-and-rescaled P feeds dV
+              // dS = P * (keep ? dP/(1-p) : 0 - D) and the dropped, rescaled P feeds dV.  Here pv already is
+              // P/(1-p) (the rescale rides on the exponent: staged LSE minus log2(1/(1-p))) and dd is D*(1-p), so
+              // dS = pv * (keep ? dP : 0 - dd) and the per-element work is two selects, no multiply.
               const bool keep = drop_keep2d(kk[t], colkey, thr32);
-              dp = keep ? dp * p.drop_scale : 0.f;
-              pd = keep ? pv * p.drop_scale : 0.f;
+              dp = keep ? dp : 0.f;
+              pd = keep ? pv : 0.f;
             }
             pt[e] = pd;
             ds[e] = pv * (dp - dd[t]);
@@ -316,9 +320,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       // stage LSE (times log2e), D and the dropout row keys for the 128 queries of this block; the
       // global loads were issued one iteration ahead (pre_val), so nobody stalls on them here
       if (tid < AB_BLK) {
-        sLSE[tid] = pre_val * 1.4426950408889634f;
+        sLSE[tid] = pre_val * 1.4426950408889634f - lg_rescale;
       } else {
-        sD[tid - AB_BLK] = pre_val;
+        sD[tid - AB_BLK] = pre_val * inv_rescale;
         if (drop) sKey[tid - AB_BLK] = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + q0 + tid - AB_BLK);
       }
       pre_val = load_stat(i + 1);

@@ -282,13 +282,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
           pv[i] = e;
         }
         if (drop) {
+          // keep / drop only: the 1/(1-p) rescale of the kept probabilities is applied once, to the final O
 #pragma unroll
           for (int t4 = 0; t4 < 32; t4 += 4) {
             const uint4 b4 = *reinterpret_cast<const uint4*>(colkeys + c * 32 + t4);
-            pv[t4 + 0] = drop_keep2d(rowkey, b4.x, thr32) ? pv[t4 + 0] * p.drop_scale : 0.f;
-            pv[t4 + 1] = drop_keep2d(rowkey, b4.y, thr32) ? pv[t4 + 1] * p.drop_scale : 0.f;
-            pv[t4 + 2] = drop_keep2d(rowkey, b4.z, thr32) ? pv[t4 + 2] * p.drop_scale : 0.f;
-            pv[t4 + 3] = drop_keep2d(rowkey, b4.w, thr32) ? pv[t4 + 3] * p.drop_scale : 0.f;
+            pv[t4 + 0] = drop_keep2d(rowkey, b4.x, thr32) ? pv[t4 + 0] : 0.f;
+            pv[t4 + 1] = drop_keep2d(rowkey, b4.y, thr32) ? pv[t4 + 1] : 0.f;
+            pv[t4 + 2] = drop_keep2d(rowkey, b4.z, thr32) ? pv[t4 + 2] : 0.f;
+            pv[t4 + 3] = drop_keep2d(rowkey, b4.w, thr32) ? pv[t4 + 3] : 0.f;
           }
         }
         // 32 keys = 4 x 16-byte chunks of the 128-byte swizzled row; chunk index XOR (row & 7)
@@ -343,7 +344,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       const float m = fmaxf(m_ref, m1);
       const float a0 = exp2f(m_ref - m), a1 = exp2f(m1 - m);
       const float l = l_run * a0 + l1 * a1;
-      const float inv = l > 0.f ? 1.f / l : 0.f;
+      const float inv = l > 0.f ? p.drop_scale / l : 0.f;   // drop_scale = 1/(1-p): dropout rescale of P, folded in here
       if (qrow < p.T) {
         __nv_bfloat16* dst = p.out + static_cast<size_t>(row_base + qrow) * p.d + h * AT_HD;
 #pragma unroll
