@@ -167,6 +167,10 @@ class NativeOps:
                                              seed, _stream()), "attention_fwd")
         self.launches += 1
 
+    def set_attention_fwd_variant(self, lazy: int) -> int:
+        """1 = lazy rescale with O in tensor memory (default), 0 = exact per-block rescale; returns the old value."""
+        return int(self.lib.b200_set_attention_fwd_variant(int(lazy)))
+
     def attention_bwd(self, qkv, out, dout, lse, dqkv, D, dq_acc, B, T, H, hd, causal=False, drop_p=0.0,
                       seed=0, have_d=False, acc_is_zero=False) -> None:
         """``have_d``: D was already produced (EPI_ROWDOT of the out-proj dgrad); ``acc_is_zero``: dq_acc holds

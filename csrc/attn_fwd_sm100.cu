@@ -24,6 +24,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <type_traits>
 
@@ -55,6 +56,14 @@ struct AttnFwdParams {
   const uint32_t* seed_ptr;
 };
 
+// LAZY = false: every softmax thread keeps its O row in registers and folds each block's P V product in with the
+//   exact running-max rescale (the round-1 kernel).
+// LAZY = true: O accumulates in tensor memory across the blocks of a warpgroup (the P V MMAs accumulate), the S row
+//   stays in registers between the max and the exponentials (one TMEM read instead of two), and the reference
+//   maximum m_ref only moves - with a rescale of the O row in TMEM - when a block's maximum exceeds it by more than 8
+//   (log2 domain): probabilities are then at most 2^8 before normalisation, exact in fp32 and harmless in bf16, and
+//   after the first blocks almost no block pays for a rescale.
+template <bool LAZY>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
   // SWIZZLE_128B tiles need 1024-byte alignment; declaring the alignment (instead of rounding the
@@ -181,7 +190,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
         for (int k = 0; k < AT_BN / 16; ++k)
           umma_bf16_ss(tmem_base + 256 + w * 64,
                        umma_smem_desc(aP + (k >> 2) * (AT_BM * 128) + (k & 3) * 32, 16, 1024),
-                       umma_smem_desc(aV + k * 2048, AT_BN * 128, 1024), idesc_o, k ? 1u : 0u);
+                       umma_smem_desc(aV + k * 2048, AT_BN * 128, 1024), idesc_o,
+                       (k || (LAZY && j >= 2)) ? 1u : 0u);   // LAZY: later blocks add onto the warpgroup's O
         umma_commit(&v_empty[vs]);
         umma_commit(&o_full[w]);
         if (++vs == AT_KV_STAGES) { vs = 0; vph ^= 1; }
@@ -310,6 +320,95 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       m_prev = m_new;
     };
 
+    // LAZY variant of one key block (see the kernel comment).  Uses m_ref as the only maximum.
+    auto block_body_lazy = [&](auto mask_c, int k0, int limit) {
+      constexpr bool MASK = decltype(mask_c)::value;
+      const uint32_t* colkeys = sColKey + (w * 2 + (n_done & 1)) * 128;
+      if (drop) {
+        sColKey[(w * 2 + (n_done & 1)) * 128 + r] = drop_colkey(seed, static_cast<uint32_t>(bh) * p.T + k0 + r);
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + w) : "memory");
+      }
+      // ---- the whole S row of this thread: TMEM -> registers, once ----------------------------
+      uint32_t sv[4][32];
+      tmem_ld_32x32b_x32(tS, sv[0]);
+      tmem_ld_32x32b_x32(tS + 32, sv[1]);
+      tmem_ld_32x32b_x32(tS + 64, sv[2]);
+      tmem_ld_32x32b_x32(tS + 96, sv[3]);
+      tmem_ld_wait();
+      float mx[4] = {NEG_BIG, NEG_BIG, NEG_BIG, NEG_BIG};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          if (MASK) {
+            if (k0 + c * 32 + i >= limit) sv[c][i] = __float_as_uint(NEG_BIG);   // exp2 of it is 0 below
+          }
+          mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sv[c][i]));
+        }
+      }
+      const float m_blk = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
+      // the previous P V of this warpgroup read the P buffer written below and produced the O that may be rescaled
+      if (n_done > 0) {
+        mbar_wait(&o_full[w], oph);
+        oph ^= 1;
+        tc_fence_after();
+      }
+      const bool grow = m_blk > m_ref + 8.f;            // first block: m_ref = NEG_BIG
+      if (__any_sync(0xffffffffu, grow)) {              // tcgen05.ld / st are warp-wide: rows that stay use alpha = 1
+        const float m_new = grow ? m_blk : m_ref;
+        const float alpha = exp2f(m_ref - m_new);       // first block: 0
+        if (n_done > 0) {
+#pragma unroll
+          for (int ch = 0; ch < AT_HD / 16; ++ch) {
+            uint32_t v[16];
+            tmem_ld_32x32b_x16(tO + ch * 16, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            tmem_st_32x32b_x16(tO + ch * 16, v);
+          }
+          tmem_st_wait();
+        }
+        l_run *= alpha;
+        m_ref = m_new;
+      }
+      // ---- P = exp2(s*scale - m_ref), row sum, bf16 -> swizzled smem --------------------------
+      float rs[4] = {0.f, 0.f, 0.f, 0.f};
+      const float neg_m = -m_ref;
+#pragma unroll
+      for (int c = 0; c < AT_BN / 32; ++c) {
+        float pv[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float e = exp2f(fmaf(__uint_as_float(sv[c][i]), p.scale_log2, neg_m));
+          rs[i & 3] += e;
+          pv[i] = e;
+        }
+        if (drop) {
+#pragma unroll
+          for (int t4 = 0; t4 < 32; t4 += 4) {
+            const uint4 b4 = *reinterpret_cast<const uint4*>(colkeys + c * 32 + t4);
+            pv[t4 + 0] = drop_keep2d(rowkey, b4.x, thr32) ? pv[t4 + 0] : 0.f;
+            pv[t4 + 1] = drop_keep2d(rowkey, b4.y, thr32) ? pv[t4 + 1] : 0.f;
+            pv[t4 + 2] = drop_keep2d(rowkey, b4.z, thr32) ? pv[t4 + 2] : 0.f;
+            pv[t4 + 3] = drop_keep2d(rowkey, b4.w, thr32) ? pv[t4 + 3] : 0.f;
+          }
+        }
+        uint8_t* dst = myP + (c >> 1) * (AT_BM * 128);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 u;
+          u.x = pack_bf16x2(pv[g * 8 + 0], pv[g * 8 + 1]);
+          u.y = pack_bf16x2(pv[g * 8 + 2], pv[g * 8 + 3]);
+          u.z = pack_bf16x2(pv[g * 8 + 4], pv[g * 8 + 5]);
+          u.w = pack_bf16x2(pv[g * 8 + 6], pv[g * 8 + 7]);
+          const int chunk = ((c & 1) * 4 + g) ^ (r & 7);
+          *reinterpret_cast<uint4*>(dst + chunk * 16) = u;
+        }
+      }
+      l_run += (rs[0] + rs[1]) + (rs[2] + rs[3]);
+    };
+
     for (int j = w; j < nkv; j += 2) {
       mbar_wait(&s_full[w], sph);
       sph ^= 1;
@@ -318,16 +417,35 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       const bool need_mask = (k0 + AT_BN > p.T) || (p.causal && j == qb);
       if (need_mask) {
         const int limit = p.causal ? min(p.T, qrow + 1) : p.T;
-        block_body(std::true_type{}, k0, limit);
+        if constexpr (LAZY) block_body_lazy(std::true_type{}, k0, limit);
+        else block_body(std::true_type{}, k0, limit);
       } else {
-        block_body(std::false_type{}, k0, 0);
+        if constexpr (LAZY) block_body_lazy(std::false_type{}, k0, 0);
+        else block_body(std::false_type{}, k0, 0);
       }
       tc_fence_before();
       fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core
       mbar_arrive(&p_full[w]);
       ++n_done;
     }
-    if (n_done > 0) accumulate_prev();
+    if constexpr (LAZY) {
+      if (n_done > 0) {          // the warpgroup's O (relative to m_ref) leaves tensor memory once
+        mbar_wait(&o_full[w], oph);
+        oph ^= 1;
+        tc_fence_after();
+        uint32_t v0[32], v1[32];
+        tmem_ld_32x32b_x32(tO, v0);
+        tmem_ld_32x32b_x32(tO + 32, v1);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          o[i] = __uint_as_float(v0[i]);
+          o[32 + i] = __uint_as_float(v1[i]);
+        }
+      }
+    } else {
+      if (n_done > 0) accumulate_prev();
+    }
 
     // ---- merge the two warpgroups and write out -------------------------------------------
     // warpgroup 1 parks (m, l, O) in shared memory (its own P buffer is idle by now).
@@ -377,6 +495,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
 
 using namespace b200;
 
+// 1 = lazy rescale with O in tensor memory (default), 0 = exact per-block rescale with O in registers.
+// B200BENCH_ATTN_FWD=exact picks 0 at start-up; b200_set_attention_fwd_variant switches at run time (tests, A/B).
+static int& attn_fwd_variant() {
+  static int v = [] {
+    const char* e = getenv("B200BENCH_ATTN_FWD");
+    return (e && e[0] == 'e') ? 0 : 1;
+  }();
+  return v;
+}
+extern "C" int b200_set_attention_fwd_variant(int lazy) {
+  const int old = attn_fwd_variant();
+  if (lazy >= 0) attn_fwd_variant() = lazy ? 1 : 0;
+  return old;
+}
+
 extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H,
                                   int head_dim, int causal, float drop_p, unsigned int seed,
                                   void* stream) {
@@ -386,11 +519,14 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B,
   int rc = make_tmap_2d_bf16(&map, qkv, static_cast<uint64_t>(B) * T, 3 * d, 3 * d, AT_BN, 64);
   if (rc) return rc;
   static bool attr_done[64] = {false};
+  const bool lazy = attn_fwd_variant() != 0;
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_done[dev & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel,
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel<false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(attn_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done[dev & 63] = true;
   }
@@ -423,5 +559,6 @@ extern "C" int b200_attention_fwd(const void* qkv, void* out, float* lse, int B,
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return static_cast<int>(cudaLaunchKernelEx(&cfg, attn_fwd_kernel, map, p));
+  return static_cast<int>(lazy ? cudaLaunchKernelEx(&cfg, attn_fwd_kernel<true>, map, p)
+                              : cudaLaunchKernelEx(&cfg, attn_fwd_kernel<false>, map, p));
 }

@@ -216,6 +216,13 @@ int main(int argc, char** argv) {
   printf("== attention timing ==\n");
   clocks::Sampler sampler;
   sampler.start();
+  for (int variant : {0, 1}) {     // forward variants: 0 = exact per-block rescale, 1 = lazy rescale with O in TMEM
+    b200_set_attention_fwd_variant(variant);
+    printf("  forward variant %d (%s)\n", variant, variant ? "lazy, default" : "exact");
+    time_case(1, 2048, 16, 0, false, 0.f);
+    time_case(1, 2048, 16, 0, false, 0.1f);
+    time_case(1, 2048, 16, 1, false, 0.f);
+  }
   time_case(1, 2048, 16, 0, false, 0.f);
   time_case(1, 2048, 16, 0, false, 0.1f);
   time_case(1, 2048, 16, 1, false, 0.f);

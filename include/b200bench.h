@@ -49,6 +49,10 @@ int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, i
  * the backward regenerates the mask from the same seed). */
 int b200_attention_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int head_dim,
                        int causal, float drop_p, unsigned int seed, void* stream);
+/* Forward variant: 1 (default) = O accumulates in tensor memory and is rescaled only when a block raises the row
+ * maximum by more than 2^8; 0 = O in registers with the exact running-max rescale after every block.  Returns the
+ * previous setting; a negative argument only queries.  Environment: B200BENCH_ATTN_FWD=exact starts with 0. */
+int b200_set_attention_fwd_variant(int lazy);
 /* dqkv [B*T, 3*H*hd] bf16 receives dQ|dK|dV.  D [B*H, T] fp32 and dq_acc [B*T, H*hd] fp32 are
  * caller-provided scratch (dq_acc is zeroed inside). */
 int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse,
