@@ -83,8 +83,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
   uint64_t* s_full = bars + 13;                    // [2]
   uint64_t* p_full = bars + 15;                    // [2]
   uint64_t* o_full = bars + 17;                    // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
-  float* merge_ml = reinterpret_cast<float*>(bars + 20);  // [2][128] m, l of warpgroup 1
+  uint64_t* s_free = bars + 19;                    // [2]  LAZY: the S row is in registers, the buffer can be refilled
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+  float* merge_ml = reinterpret_cast<float*>(bars + 22);  // [2][128] m, l of warpgroup 1
   uint32_t* sColKey = reinterpret_cast<uint32_t*>(merge_ml + 256);   // [2 warpgroups][2 buffers][128]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -110,6 +111,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       mbar_init(&s_full[w], 1);
       mbar_init(&p_full[w], 128);
       mbar_init(&o_full[w], 1);
+      mbar_init(&s_free[w], 128);
     }
     fence_mbar_init();
   }
@@ -175,13 +177,25 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       tc_fence_after();
       issue_s(0);
       if (nkv > 1) issue_s(1);
-      uint32_t pph[2] = {0, 0};
+      uint32_t pph[2] = {0, 0}, sfph[2] = {0, 0};
       for (int j = 0; j < nkv; ++j) {
         const int w = j & 1;
+        if constexpr (LAZY) {
+          // the warpgroup holds the whole S(j) row in registers: S(j+2) is computed while it is still busy with
+          // the exponentials of block j, so it never waits for scores
+          if (j + 2 < nkv) {
+            mbar_wait(&s_free[w], sfph[w]);
+            sfph[w] ^= 1;
+            tc_fence_after();
+            issue_s(w);
+          }
+        }
         mbar_wait(&p_full[w], pph[w]);  // P(j) in smem, S[w] fully read
         pph[w] ^= 1;
         tc_fence_after();
-        if (j + 2 < nkv) issue_s(w);    // next scores for this warpgroup first
+        if constexpr (!LAZY) {
+          if (j + 2 < nkv) issue_s(w);  // next scores for this warpgroup first
+        }
         mbar_wait(&v_full[vs], vph);
         tc_fence_after();
         const uint32_t aP = smem_u32(sP + w * AT_PBYTES);
@@ -335,6 +349,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       tmem_ld_32x32b_x32(tS + 64, sv[2]);
       tmem_ld_32x32b_x32(tS + 96, sv[3]);
       tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&s_free[w]);                          // the MMA warp may refill this S buffer with block j+2
       float mx[4] = {NEG_BIG, NEG_BIG, NEG_BIG, NEG_BIG};
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
