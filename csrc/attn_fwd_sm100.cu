@@ -124,6 +124,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
   pdl_wait();      // nothing below may run before the previous kernel's writes are visible
   // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384)
 
+  // LAZY with dropout: release the S buffer as soon as the row is in registers (measured: 58.6 -> 55.4 us with
+  // dropout 0.1 at the headline shape, but 45.3 -> 47.6 us without dropout, where the softmax is too short to gain)
+  const bool early_s = LAZY && p.drop_threshold != 0;
   if (warp < 4) {
     setmaxnreg_dec<40>();
   if (warp == 0) {
@@ -180,7 +183,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       uint32_t pph[2] = {0, 0}, sfph[2] = {0, 0};
       for (int j = 0; j < nkv; ++j) {
         const int w = j & 1;
-        if constexpr (LAZY) {
+        if (early_s) {
           // the warpgroup holds the whole S(j) row in registers: S(j+2) is computed while it is still busy with
           // the exponentials of block j, so it never waits for scores
           if (j + 2 < nkv) {
@@ -193,7 +196,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
         mbar_wait(&p_full[w], pph[w]);  // P(j) in smem, S[w] fully read
         pph[w] ^= 1;
         tc_fence_after();
-        if constexpr (!LAZY) {
+        if (!early_s) {
           if (j + 2 < nkv) issue_s(w);  // next scores for this warpgroup first
         }
         mbar_wait(&v_full[vs], vph);
@@ -349,8 +352,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams
       tmem_ld_32x32b_x32(tS + 64, sv[2]);
       tmem_ld_32x32b_x32(tS + 96, sv[3]);
       tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&s_free[w]);                          // the MMA warp may refill this S buffer with block j+2
+      if (early_s) {
+        tc_fence_before();
+        mbar_arrive(&s_free[w]);                        // the MMA warp may refill this S buffer with block j+2
+      }
       float mx[4] = {NEG_BIG, NEG_BIG, NEG_BIG, NEG_BIG};
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
