@@ -24,6 +24,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <type_traits>
 
@@ -60,6 +61,9 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                : "memory");
 }
 
+// EARLY: the S^T / dP^T columns are released as soon as the compute warps hold the tile in registers, so the next
+// block's scores are computed during this block's exponentials (B200BENCH_ATTN_BWD=serial selects the other order).
+template <bool EARLY>
 __global__ void __launch_bounds__(AB_THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
                 const __grid_constant__ CUtensorMap map_do, const AttnBwdParams p) {
@@ -84,7 +88,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
   uint64_t* pds_full = bars + 6;     // 1 (256 arrivals)
   uint64_t* dq_full = bars + 7;      // 1
   uint64_t* dq_empty = bars + 8;     // 1 (256 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* sdp_free = bars + 9;     // 1 (256 arrivals): S^T / dP^T of the block are in registers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nblk = (p.T + AB_BLK - 1) / AB_BLK;
@@ -107,6 +112,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     mbar_init(pds_full, 256);
     mbar_init(dq_full, 1);
     mbar_init(dq_empty, 256);
+    mbar_init(sdp_free, 256);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -166,10 +172,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       if (i_begin < nblk) issue_sdp();
       for (int i = i_begin; i < nblk; ++i) {
         const int buf = (i - i_begin) & 1;      // P/dS buffer and Q/dO stage of block i
+        if (EARLY && i + 1 < nblk) {
+          // the compute warps hold S^T(i) / dP^T(i) in registers: the next block's scores are computed while they
+          // are still busy with the exponentials of this one, so they never wait for the tensor cores
+          mbar_wait(sdp_free, it_ph);
+          tc_fence_after();
+          issue_sdp();
+        }
         mbar_wait(pds_full, it_ph);             // P^T(i), dS^T(i) are in shared memory; S/dP TMEM is free
         tc_fence_after();
-        if (i + 1 < nblk) issue_sdp();          // next block's scores first: the compute warps start on
-                                                // them while the three products below run
+        if (!EARLY && i + 1 < nblk) issue_sdp();   // next block's scores first: the compute warps start
+                                                         // on them while the three products below run
         mbar_wait(dq_empty, it_ph ^ 1);         // previous dQ tile has been drained
         tc_fence_after();
         const uint32_t aQ = smem_u32(sQ + buf * AB_TILE), aDO = smem_u32(sDO + buf * AB_TILE);
@@ -226,13 +239,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       uint32_t vs[2][32], vd[2][32];
       tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + wg * 64, vs[0]);
       tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + wg * 64, vd[0]);
+      if constexpr (EARLY) {
+        // the whole tile goes to registers at once; the S / dP columns in tensor memory are free from here on
+        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + wg * 64 + 32, vs[1]);
+        tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + wg * 64 + 32, vd[1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(sdp_free);
+      }
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         const int col0 = wg * 64 + c * 32;
-        tmem_ld_wait();
-        if (c == 0) {
-          tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + wg * 64 + 32, vs[1]);
-          tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + wg * 64 + 32, vd[1]);
+        if constexpr (!EARLY) {
+          tmem_ld_wait();
+          if (c == 0) {
+            tmem_ld_32x32b_x32(tmem_base + t_lane + TC_S + wg * 64 + 32, vs[1]);
+            tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DP + wg * 64 + 32, vd[1]);
+          }
         }
         float pt[32], ds[32];
 #pragma unroll
@@ -450,8 +473,10 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_done[dev & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel,
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel<true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(attn_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done[dev & 63] = true;
   }
@@ -483,6 +508,10 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
   }
   p.drop_seed = seed;
   p.seed_ptr = step_seed_ptr();
+  static const int early = [] {            // B200BENCH_ATTN_BWD=serial: S / dP of the next block only after P / dS
+    const char* e = getenv("B200BENCH_ATTN_BWD");
+    return (e && e[0] == 's') ? 0 : 1;
+  }();
   const int grid = B * H * ((T + AB_BLK - 1) / AB_BLK);
   {
     cudaLaunchConfig_t cfg = {};
@@ -495,7 +524,8 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t le = cudaLaunchKernelEx(&cfg, attn_bwd_kernel, map_qkv, map_do, p);
+    cudaError_t le = early ? cudaLaunchKernelEx(&cfg, attn_bwd_kernel<true>, map_qkv, map_do, p)
+                           : cudaLaunchKernelEx(&cfg, attn_bwd_kernel<false>, map_qkv, map_do, p);
     if (le != cudaSuccess) return static_cast<int>(le);
   }
   {
