@@ -225,8 +225,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     const float lg_rescale = drop ? log2f(p.drop_scale) : 0.f;   // drop_scale = 1/(1-p)
     const float inv_rescale = drop ? 1.f / p.drop_scale : 1.f;
     const uint32_t colkey = drop_colkey(seed, static_cast<uint32_t>(bh) * p.T + krow);   // b(k) of this thread's key
-    uint8_t* rowP = nullptr;   // set per query block: P/dS buffer (i & 1)
-    uint8_t* rowS = nullptr;
+    // 32-bit shared addresses, taken once (see lds_v4 / sts_v4 in sm100_ptx.cuh for why)
+    const uint32_t aLSE = smem_u32(sLSE), aD = smem_u32(sD), aKey = smem_u32(sKey);
+    const uint32_t aP0 = smem_u32(sP), aDS0 = smem_u32(sDS);
+    uint32_t rowP = 0;         // set per query block: P/dS buffer (i & 1)
+    uint32_t rowS = 0;
     uint32_t it_ph = 0;
 
     // One (key block, query block) tile for this thread's key row and its 64 query columns.
@@ -260,12 +263,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
         float pt[32], ds[32];
 #pragma unroll
         for (int e4 = 0; e4 < 32; e4 += 4) {
-          const float4 l4 = *reinterpret_cast<const float4*>(sLSE + col0 + e4);
-          const float4 d4 = *reinterpret_cast<const float4*>(sD + col0 + e4);
-          const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, dd[4] = {d4.x, d4.y, d4.z, d4.w};
+          const uint4 l4 = lds_v4(aLSE + (col0 + e4) * 4);
+          const uint4 d4 = lds_v4(aD + (col0 + e4) * 4);
+          const float ls[4] = {__uint_as_float(l4.x), __uint_as_float(l4.y), __uint_as_float(l4.z), __uint_as_float(l4.w)};
+          const float dd[4] = {__uint_as_float(d4.x), __uint_as_float(d4.y), __uint_as_float(d4.z), __uint_as_float(d4.w)};
           uint32_t kk[4] = {0, 0, 0, 0};
           if (DROP) {
-            const uint4 k4 = *reinterpret_cast<const uint4*>(sKey + col0 + e4);
+            const uint4 k4 = lds_v4(aKey + (col0 + e4) * 4);
             kk[0] = k4.x; kk[1] = k4.y; kk[2] = k4.z; kk[3] = k4.w;
           }
 #pragma unroll
@@ -298,12 +302,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
           u.y = pack_bf16x2(pt[g * 8 + 2], pt[g * 8 + 3]);
           u.z = pack_bf16x2(pt[g * 8 + 4], pt[g * 8 + 5]);
           u.w = pack_bf16x2(pt[g * 8 + 6], pt[g * 8 + 7]);
-          *reinterpret_cast<uint4*>(rowP + chunk * 16) = u;
+          sts_v4(rowP + chunk * 16, u);
           u.x = pack_bf16x2(ds[g * 8 + 0], ds[g * 8 + 1]);
           u.y = pack_bf16x2(ds[g * 8 + 2], ds[g * 8 + 3]);
           u.z = pack_bf16x2(ds[g * 8 + 4], ds[g * 8 + 5]);
           u.w = pack_bf16x2(ds[g * 8 + 6], ds[g * 8 + 7]);
-          *reinterpret_cast<uint4*>(rowS + chunk * 16) = u;
+          sts_v4(rowS + chunk * 16, u);
         }
       }
     };
@@ -338,15 +342,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
     for (int i = i_begin; i < nblk; ++i) {
       const int q0 = i * AB_BLK;
       const int buf = (i - i_begin) & 1;
-      rowP = sP + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
-      rowS = sDS + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
+      rowP = aP0 + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
+      rowS = aDS0 + buf * AB_PBYTES + wg * (AB_BLK * 128) + r * 128;
       // stage LSE (times log2e), D and the dropout row keys for the 128 queries of this block; the
       // global loads were issued one iteration ahead (pre_val), so nobody stalls on them here
       if (tid < AB_BLK) {
-        sLSE[tid] = pre_val * 1.4426950408889634f - lg_rescale;
+        sts_u32(aLSE + tid * 4, __float_as_uint(pre_val * 1.4426950408889634f - lg_rescale));
       } else {
-        sD[tid - AB_BLK] = pre_val * inv_rescale;
-        if (drop) sKey[tid - AB_BLK] = drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + q0 + tid - AB_BLK);
+        sts_u32(aD + (tid - AB_BLK) * 4, __float_as_uint(pre_val * inv_rescale));
+        if (drop) sts_u32(aKey + (tid - AB_BLK) * 4, drop_rowkey(seed, static_cast<uint32_t>(bh) * p.T + q0 + tid - AB_BLK));
       }
       pre_val = load_stat(i + 1);
       asm volatile("bar.sync 1, 256;" ::: "memory");

@@ -288,6 +288,25 @@ __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
 }
 
 // ----------------------------------------------------------------------------------------
+// Shared-memory accesses through an explicit 32-bit shared address (smem_u32 of the pointer, taken once).  Inside
+// long loops this keeps the compiler from re-deriving the shared window base (S2UR SR_CgaCtaId) every iteration in a
+// uniform register that earlier global reductions still hold as their descriptor - which made every warp wait for
+// its red.global.add to retire at the top of each iteration of the attention backward.
+// ----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// ----------------------------------------------------------------------------------------
 // tcgen05: TMEM <-> registers.  32x32b shape: thread t of the warp owns TMEM lane
 // (lane_base + t), registers hold consecutive 32-bit columns.  A warp may only touch the lane
 // quarter  32*(warp_id % 4) .. +31.
