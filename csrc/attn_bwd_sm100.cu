@@ -53,6 +53,7 @@ struct AttnBwdParams {
   float drop_scale;
   uint32_t drop_seed;
   const uint32_t* seed_ptr;
+  int diag_skip_dq;   // diagnostics only (B200BENCH_ATTN_BWD=noreduce): leave out the dQ reductions, result is wrong
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -320,7 +321,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap map_qkv,
       tmem_ld_32x32b_x32(tmem_base + t_lane + TC_DQ + wg * 32, v);
       tmem_ld_wait();
       const int q = qi * AB_BLK + r;
-      if (q < p.T) {
+      // Every key block adds into dQ: red.global.add.v4.f32 from registers.  Measured at the headline shape: leaving
+      // the reductions out takes the kernel from 126 to 111 us; handing them to the copy engine instead was slower
+      // (one 128-byte bulk reduce-add per thread from shared memory: 157 us - its addresses are uniform registers, so
+      // a warp issues them lane by lane; one [32 x 32] fp32 tile reduce-add per warp through a tensor map: 141 us).
+      if (q < p.T && !p.diag_skip_dq) {
         float* dst = p.dq_acc + static_cast<size_t>(row_base + q) * p.d + h * AB_HD + wg * 32;
 #pragma unroll
         for (int e = 0; e < 32; e += 4)
@@ -516,6 +521,11 @@ static int attention_bwd_impl(const void* qkv, const void* out, const void* dout
     const char* e = getenv("B200BENCH_ATTN_BWD");
     return (e && e[0] == 's') ? 0 : 1;
   }();
+  static const int skip_dq = [] {
+    const char* e = getenv("B200BENCH_ATTN_BWD");
+    return (e && e[0] == 'n') ? 1 : 0;
+  }();
+  p.diag_skip_dq = skip_dq;
   const int grid = B * H * ((T + AB_BLK - 1) / AB_BLK);
   {
     cudaLaunchConfig_t cfg = {};
