@@ -122,6 +122,11 @@ def train(args: Any) -> Dict[str, Any]:
     profile = getattr(args, "profile", False)
     nvtx = bool(getattr(args, "nvtx", False)) and device.type == "cuda"
 
+    sampler = None
+    if device.type == "cuda":             # SM clock / throttle-reason record of the run (rank-local GPU, NVML thread)
+        from .utils.clocks import ClockSampler
+        sampler = ClockSampler(device.index if device.index is not None else 0).start()
+
     for step in range(args.steps):
         if nvtx:
             torch.cuda.nvtx.range_push(f"step {step}" + (" (warm-up)" if step < args.warmup_steps else ""))
@@ -143,6 +148,7 @@ def train(args: Any) -> Dict[str, Any]:
 
     if device.type == "cuda":
         torch.cuda.synchronize(device)
+    clocks = sampler.stop() if sampler is not None else None
     ctx.barrier()                                                       # TH:396-397
 
     step_times = timer.times()
@@ -168,6 +174,8 @@ def train(args: Any) -> Dict[str, Any]:
         "attn": getattr(args, "attn", "bidir"),
         "gpu_launches_per_step": engine.kernel_launches_per_step(),
     }
+    if clocks is not None:
+        extra["clocks"] = {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons", "power_w_max", "samples")}
     try:                                  # closed-form work of one micro-step vs the measured peaks (analysis/roofline.py)
         from .analysis.roofline import roofline
 
